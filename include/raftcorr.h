@@ -1,0 +1,120 @@
+/*
+ * raftcorr.h — C ABI of libraftcorr_b200.so: RAFT's correlation hot path on B200 (sm_100a).
+ *
+ * The reference (zhaoyuzhi/PyTorch-RAFT) reaches this path through Python only
+ * (core/corr.py) and through one pybind11 extension (alt_cuda_corr/correlation.cpp:51-54).
+ * This header is the boundary a binding would use instead: plain pointers, sizes and a
+ * cudaStream_t, no torch types.  pytorch-raft_b200/raftcorr_b200/_capi.py binds it with ctypes;
+ * INTEGRATION.md shows the binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative RAFTCORR_E_* for a rejected argument,
+ *    or a positive cudaError_t; raftcorr_last_error() gives the text (thread-local).
+ *  - no function allocates device memory, synchronises the device or changes the current
+ *    device; kernels are enqueued on `stream` (a cudaStream_t passed as void*; NULL = the
+ *    legacy default stream).  All pointers are device pointers on the current device unless
+ *    the name says host.
+ *  - re-entrant: no mutable global state (nn.DataParallel calls it from one thread per GPU).
+ */
+#ifndef RAFTCORR_H_
+#define RAFTCORR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RAFTCORR_MAX_LEVELS 4
+
+#define RAFTCORR_E_INVALID (-1)     /* bad pointer / size / enum                     */
+#define RAFTCORR_E_UNSUPPORTED (-2) /* valid request this build cannot serve         */
+#define RAFTCORR_E_WORKSPACE (-3)   /* workspace too small                           */
+#define RAFTCORR_E_DRIVER (-4)      /* CUDA driver entry point (tensor maps) missing */
+
+/* How a pixel coordinate becomes a sampling index (DESIGN.md "coordinate semantics").
+ * core/utils/utils.py:61-62 normalises to [-1,1] and ATen's grid_sampler un-normalises again;
+ * that fp32 round trip moves floor() on ~8 % of integer-grid taps, so it is replayed exactly. */
+#define RAFTCORR_COORD_ATEN_CPU 0  /* 2x/(W-1): true division, as ATen's CPU kernels do it      */
+#define RAFTCORR_COORD_ATEN_CUDA 1 /* 2x*(1/(W-1)): as ATen's CUDA div-by-scalar kernel does it */
+#define RAFTCORR_COORD_DIRECT 2    /* floor(x) directly: alt_cuda_corr/correlation_kernel.cu:66-76 */
+
+/* Arithmetic of the all-pairs contraction (core/corr.py:58 is an fp32 cuBLAS SGEMM). */
+#define RAFTCORR_PREC_FP32 0 /* fp32-accurate: <=1e-5 of max|ref| (north_star "fp32 mode")   */
+#define RAFTCORR_PREC_BF16 1 /* one bf16 tcgen05 pass, fp32 accumulate: <=1e-2 of max|ref|   */
+#define RAFTCORR_PREC_TF32 2 /* one tf32 tcgen05 pass, fp32 accumulate: <=1e-2 of max|ref|   */
+
+/* One pyramid level: `images` 2-D fp32 images of H x W, row pitch and image stride in elements.
+ * This is core/corr.py:21-27's corr_pyramid[l] (shape (B*H1*W1, 1, H, W)) with explicit
+ * strides, so that rows can be padded to 16 bytes for TMA. */
+typedef struct raftcorr_level {
+  float* data;
+  int32_t H, W;
+  int64_t pitch;        /* elements between rows   (>= W)        */
+  int64_t image_stride; /* elements between images (>= H*pitch)  */
+} raftcorr_level;
+
+int raftcorr_version(void);
+const char* raftcorr_last_error(void);
+
+/* Level sizes of core/corr.py:25-27 (avg_pool2d floors) and the padded layout this library
+ * prefers: pitch rounded up to 4 floats.  Fills H/W/pitch/image_stride of levels[0..L) (data
+ * untouched) and returns the number of floats each level needs in floats_per_level[]. */
+int raftcorr_pyramid_layout(int B, int H, int W, int num_levels, raftcorr_level* levels,
+                            int64_t* floats_per_level);
+
+/* ---- (1) all-pairs volume + pyramid: replaces CorrBlock.__init__ / CorrBlock.corr
+ *      (core/corr.py:13-27, 52-60).  fmap1/fmap2: (B,D,H,W) fp32 NCHW contiguous.
+ *      levels[l] for l<L receive mean-pooled fmap1^T.fmap2/sqrt(D); image index = b*H*W + y*W + x
+ *      of the fmap1 pixel.  workspace: raftcorr_build_workspace_bytes() bytes, 256-byte aligned. */
+int64_t raftcorr_build_workspace_bytes(int B, int D, int H, int W, int precision);
+int raftcorr_build_pyramid(const float* fmap1, const float* fmap2, int B, int D, int H, int W,
+                           int num_levels, const raftcorr_level* levels, int precision,
+                           void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ---- (2) 4-level (2r+1)^2 bilinear window lookup: replaces CorrBlock.__call__
+ *      (core/corr.py:29-50) including bilinear_sampler (core/utils/utils.py:57-65) and
+ *      grid_sample(align_corners=True, zero padding).
+ *      coords: (B,2,H,W) fp32, ch0=x ch1=y.  out: (B, L*(2r+1)^2, H, W) fp32 contiguous,
+ *      channel = l*(2r+1)^2 + i*(2r+1) + j, i moving x and j moving y. */
+int raftcorr_lookup_fwd(const raftcorr_level* levels, int num_levels, const float* coords,
+                        float* out, int B, int H, int W, int radius, int coord_mode, void* stream);
+
+/* Backward of (2) (the reference gets it from autograd: GridSampler2DBackward0, SURVEY.md §8
+ * a-10).  grad_levels[l] must be zero-filled by the caller and are accumulated into with
+ * atomics (several lookups may accumulate into the same buffers).  grad_coords (B,2,H,W) may be
+ * NULL (RAFT detaches coords, core/raft.py:123); when given it is overwritten. */
+int raftcorr_lookup_bwd(const raftcorr_level* levels, const raftcorr_level* grad_levels,
+                        int num_levels, const float* coords, const float* grad_out,
+                        float* grad_coords, int B, int H, int W, int radius, int coord_mode,
+                        void* stream);
+
+/* Backward of (1): grad_fmap1/2 (B,D,H,W) from the accumulated d(pyramid)
+ * (AvgPool2DBackward0 x3, DivBackward0, BmmBackward0 of core/corr.py:21-27,52-60).
+ * workspace: raftcorr_build_bwd_workspace_bytes() bytes. */
+int64_t raftcorr_build_bwd_workspace_bytes(int B, int D, int H, int W);
+int raftcorr_build_bwd(const raftcorr_level* grad_levels, int num_levels, const float* fmap1,
+                       const float* fmap2, float* grad_fmap1, float* grad_fmap2, int B, int D,
+                       int H, int W, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ---- (3) on-the-fly correlation: replaces alt_cuda_corr.forward / .backward
+ *      (alt_cuda_corr/correlation.cpp:23-48, correlation_kernel.cu:18-324).
+ *      fmap1: (B,H1,W1,C) NHWC, fmap2: (B,H2,W2,C) NHWC, coords: (B,1,H1,W1,2) last dim (x,y),
+ *      corr: (B,1,(2r+1)^2,H1,W1), multiplied by `scale` (the reference kernel is unscaled:
+ *      scale=1; core/corr.py:91 divides by sqrt(C) afterwards). */
+int raftcorr_alt_fwd(const float* fmap1, const float* fmap2, const float* coords, float* corr,
+                     int B, int H1, int W1, int H2, int W2, int C, int radius, int coord_mode,
+                     float scale, void* stream);
+/* fmap1_grad/fmap2_grad must be zero-filled by the caller (accumulated with atomics);
+ * coords_grad may be NULL.  The reference returns coords_grad as all zeros
+ * (correlation_kernel.cu:130,307,323); this library fills it (documented superset). */
+int raftcorr_alt_bwd(const float* fmap1, const float* fmap2, const float* coords,
+                     const float* corr_grad, float* fmap1_grad, float* fmap2_grad,
+                     float* coords_grad, int B, int H1, int W1, int H2, int W2, int C, int radius,
+                     int coord_mode, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAFTCORR_H_ */

@@ -1,0 +1,101 @@
+"""Drop-in replacement for the reference's ``core/corr.py`` (zhaoyuzhi/PyTorch-RAFT).
+
+Put this directory ahead of the reference's ``core/`` on ``sys.path`` and ``core/raft.py`` runs
+unchanged: it does ``from corr import CorrBlock, AlternateCorrBlock`` (raft.py:8), constructs
+``CorrBlock(fmap1, fmap2, radius=r)`` once per frame pair (raft.py:104-107) and calls
+``corr_fn(coords1)`` once per refinement iteration (raft.py:124).
+
+Same names, arguments, shapes and error behaviour as the reference; all arithmetic runs in
+libraftcorr_b200.so (hand-written sm_100a kernels).  There is no CPU or ATen fallback: tensors
+must live on a CUDA device and the extension must be built, otherwise the call raises.
+
+Extras (keyword-only, all optional): ``precision`` ('bf16' default | 'tf32' | 'fp32') selects the
+arithmetic of the all-pairs contraction, ``coord_mode`` ('aten_cpu' default | 'aten_cuda' |
+'direct') selects which evaluation of the reference's coordinate round trip is replayed
+(DESIGN.md).  Environment variables RAFTCORR_PRECISION / RAFTCORR_COORD_MODE set the defaults.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn.functional as F
+
+from raftcorr_b200 import ops
+
+
+class CorrBlock:
+    """core/corr.py:12-60.  ``corr_pyramid`` keeps the reference's shapes
+    ``(B*H*W, 1, H_l, W_l)`` (strided views: rows are padded to 16 bytes for TMA)."""
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, *, precision=None, coord_mode=None):
+        self.num_levels = num_levels
+        self.radius = radius
+        self._coord_mode = ops.resolve_coord_mode(coord_mode)
+        self._holder = {}
+        self._token = None
+        if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
+            self._token, *views = ops.BuildFn.apply(fmap1, fmap2, num_levels,
+                                                    ops.resolve_precision(precision), self._holder)
+            self.corr_pyramid = list(views)
+        else:
+            self._holder["pyr"] = ops.build_pyramid(fmap1, fmap2, num_levels, precision)
+            self.corr_pyramid = self._holder["pyr"].views()
+
+    def __call__(self, coords):
+        needs_graph = torch.is_grad_enabled() and (
+            coords.requires_grad or (self._token is not None and self._token.requires_grad))
+        if needs_graph:
+            token = self._token
+            if token is None:
+                token = torch.zeros(1, dtype=torch.float32, device=coords.device)
+            return ops.LookupFn.apply(coords, token, self._holder, self.radius, self._coord_mode)
+        return ops.lookup(self._holder["pyr"], coords, self.radius, self._coord_mode)
+
+    @staticmethod
+    def corr(fmap1, fmap2, *, precision=None):
+        """core/corr.py:52-60: the all-pairs volume (B,H,W,1,H,W), scaled by 1/sqrt(D)."""
+        B, D, H, W = fmap1.shape
+        pyr = ops.build_pyramid(fmap1, fmap2, 1, precision)
+        return pyr.views()[0].reshape(B, H, W, 1, H, W)
+
+
+class AlternateCorrBlock:
+    """core/corr.py:63-91: memory-lean path that never materialises the volume.
+
+    ``pyramid`` keeps the reference's list of pooled (fmap1, fmap2) pairs (num_levels+1 entries,
+    corr.py:68-72).  The NHWC copies the reference re-creates on every call (corr.py:82-83) are
+    made once here.  Each level is one launch of the on-the-fly kernel; the 1/sqrt(D) of
+    corr.py:91 is folded into it.  ``coord_mode`` defaults to CorrBlock's coordinate semantics
+    so both blocks produce identical zero-padding masks; pass 'direct' for the reference CUDA
+    kernel's floor(coords) behaviour (correlation_kernel.cu:66-76)."""
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, *, coord_mode=None):
+        self.num_levels = num_levels
+        self.radius = radius
+        self._coord_mode = ops.resolve_coord_mode(coord_mode)
+        self.pyramid = [(fmap1, fmap2)]
+        for _ in range(self.num_levels):
+            fmap1 = F.avg_pool2d(fmap1, 2, stride=2)
+            fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
+            self.pyramid.append((fmap1, fmap2))
+        self._f1 = self.pyramid[0][0].permute(0, 2, 3, 1).contiguous()
+        self._f2 = [self.pyramid[i][1].permute(0, 2, 3, 1).contiguous() for i in range(num_levels)]
+
+    def __call__(self, coords):
+        coords = coords.permute(0, 2, 3, 1)
+        B, H, W, _ = coords.shape
+        dim = self._f1.shape[-1]
+        scale = 1.0 / math.sqrt(dim)
+        graph = torch.is_grad_enabled() and (coords.requires_grad or self._f1.requires_grad
+                                             or self._f2[0].requires_grad)
+        corr_list = []
+        for i in range(self.num_levels):
+            coords_i = (coords / 2 ** i).reshape(B, 1, H, W, 2).contiguous()
+            if graph:
+                corr = ops.AltFn.apply(self._f1, self._f2[i], coords_i, self.radius, self._coord_mode, scale)
+            else:
+                corr = ops.alt_forward(self._f1, self._f2[i], coords_i, self.radius, self._coord_mode, scale)
+            corr_list.append(corr.squeeze(1))
+        corr = torch.stack(corr_list, dim=1)
+        return corr.reshape(B, -1, H, W)

@@ -1,0 +1,187 @@
+// api.cu — the extern "C" surface declared in include/raftcorr.h: argument checks + launches.
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "common.cuh"
+
+namespace raftcorr {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int cuda_fail(cudaError_t err, const char* what) {
+  snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) at %s", (int)err, cudaGetErrorString(err), what);
+  return (int)err;
+}
+
+// launchers implemented in the kernel files
+int launch_lookup_fwd(const raftcorr_level* levels, int L, const float* coords, float* out, int B,
+                      int H, int W, int r, int mode, cudaStream_t stream);
+int launch_lookup_bwd(const raftcorr_level* levels, const raftcorr_level* glevels, int L,
+                      const float* coords, const float* gout, float* gcoords, int B, int H, int W,
+                      int r, int mode, cudaStream_t stream);
+int launch_build_fp32(const float* f1, const float* f2, int B, int D, int H, int W, int L,
+                      const raftcorr_level* levels, cudaStream_t stream);
+int64_t build_tc_workspace_bytes(int B, int D, int H, int W, int precision);
+int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W, int L,
+                    const raftcorr_level* levels, int precision, void* ws, int64_t ws_bytes,
+                    cudaStream_t stream);
+int64_t build_bwd_workspace_bytes(int B, int D, int H, int W);
+int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, const float* f2,
+                     float* g1, float* g2, int B, int D, int H, int W, void* ws, int64_t ws_bytes,
+                     cudaStream_t stream);
+int launch_alt_fwd(const float* f1, const float* f2, const float* coords, float* corr, int B, int H1,
+                   int W1, int H2, int W2, int C, int r, int mode, float scale, cudaStream_t stream);
+int launch_alt_bwd(const float* f1, const float* f2, const float* coords, const float* gcorr,
+                   float* g1, float* g2, float* gcoords, int B, int H1, int W1, int H2, int W2, int C,
+                   int r, int mode, float scale, cudaStream_t stream);
+
+static int check_levels(const raftcorr_level* levels, int L, int H, int W, const char* what) {
+  RC_REQUIRE(levels != nullptr, "%s: levels is NULL", what);
+  RC_REQUIRE(L >= 1 && L <= RAFTCORR_MAX_LEVELS, "%s: num_levels=%d not in [1,%d]", what, L,
+             RAFTCORR_MAX_LEVELS);
+  for (int l = 0; l < L; ++l) {
+    RC_REQUIRE(levels[l].data != nullptr, "%s: levels[%d].data is NULL", what, l);
+    RC_REQUIRE(levels[l].H == (H >> l) && levels[l].W == (W >> l),
+               "%s: levels[%d] is %dx%d, expected %dx%d (avg_pool2d floors)", what, l, levels[l].H,
+               levels[l].W, H >> l, W >> l);
+    RC_REQUIRE(levels[l].H >= 1 && levels[l].W >= 1, "%s: level %d is empty", what, l);
+    RC_REQUIRE(levels[l].pitch >= levels[l].W &&
+                   levels[l].image_stride >= levels[l].pitch * levels[l].H,
+               "%s: levels[%d] pitch/image_stride too small", what, l);
+  }
+  return 0;
+}
+
+static bool valid_mode(int m) { return m >= RAFTCORR_COORD_ATEN_CPU && m <= RAFTCORR_COORD_DIRECT; }
+
+}  // namespace raftcorr
+
+using namespace raftcorr;
+
+extern "C" {
+
+int raftcorr_version(void) { return 100; }
+
+const char* raftcorr_last_error(void) { return g_err; }
+
+int raftcorr_pyramid_layout(int B, int H, int W, int num_levels, raftcorr_level* levels,
+                            int64_t* floats_per_level) {
+  RC_REQUIRE(levels && floats_per_level, "pyramid_layout: NULL output");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "pyramid_layout: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(num_levels >= 1 && num_levels <= RAFTCORR_MAX_LEVELS, "pyramid_layout: num_levels=%d",
+             num_levels);
+  for (int l = 0; l < num_levels; ++l) {
+    const int Hl = H >> l, Wl = W >> l;
+    RC_REQUIRE(Hl >= 1 && Wl >= 1, "pyramid_layout: level %d of %dx%d is empty", l, H, W);
+    levels[l].H = Hl;
+    levels[l].W = Wl;
+    levels[l].pitch = (Wl + 3) & ~3;  // rows start on 16 B so TMA can address them
+    levels[l].image_stride = levels[l].pitch * Hl;
+    floats_per_level[l] = (int64_t)B * H * W * levels[l].image_stride;
+  }
+  return 0;
+}
+
+int64_t raftcorr_build_workspace_bytes(int B, int D, int H, int W, int precision) {
+  if (precision == RAFTCORR_PREC_FP32) return 0;
+  return build_tc_workspace_bytes(B, D, H, W, precision);
+}
+
+int raftcorr_build_pyramid(const float* fmap1, const float* fmap2, int B, int D, int H, int W,
+                           int num_levels, const raftcorr_level* levels, int precision,
+                           void* workspace, int64_t workspace_bytes, void* stream) {
+  RC_REQUIRE(fmap1 && fmap2, "build_pyramid: fmap pointer is NULL");
+  RC_REQUIRE(B >= 0 && D >= 1 && H >= 1 && W >= 1, "build_pyramid: bad sizes B=%d D=%d H=%d W=%d", B,
+             D, H, W);
+  RC_REQUIRE((long long)H * W <= (1 << 24), "build_pyramid: fmap too large");
+  if (int rc = check_levels(levels, num_levels, H, W, "build_pyramid")) return rc;
+  if (precision == RAFTCORR_PREC_FP32)
+    return launch_build_fp32(fmap1, fmap2, B, D, H, W, num_levels, levels, (cudaStream_t)stream);
+  RC_REQUIRE(precision == RAFTCORR_PREC_BF16 || precision == RAFTCORR_PREC_TF32,
+             "build_pyramid: unknown precision %d", precision);
+  return launch_build_tc(fmap1, fmap2, B, D, H, W, num_levels, levels, precision, workspace,
+                         workspace_bytes, (cudaStream_t)stream);
+}
+
+int raftcorr_lookup_fwd(const raftcorr_level* levels, int num_levels, const float* coords,
+                        float* out, int B, int H, int W, int radius, int coord_mode, void* stream) {
+  RC_REQUIRE(coords && out, "lookup_fwd: coords/out is NULL");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "lookup_fwd: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(radius >= 0 && radius <= 4, "lookup_fwd: radius=%d not in [0,4]", radius);
+  RC_REQUIRE(valid_mode(coord_mode), "lookup_fwd: coord_mode=%d", coord_mode);
+  if (int rc = check_levels(levels, num_levels, H, W, "lookup_fwd")) return rc;
+  return launch_lookup_fwd(levels, num_levels, coords, out, B, H, W, radius, coord_mode,
+                           (cudaStream_t)stream);
+}
+
+int raftcorr_lookup_bwd(const raftcorr_level* levels, const raftcorr_level* grad_levels,
+                        int num_levels, const float* coords, const float* grad_out,
+                        float* grad_coords, int B, int H, int W, int radius, int coord_mode,
+                        void* stream) {
+  RC_REQUIRE(coords && grad_out, "lookup_bwd: coords/grad_out is NULL");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "lookup_bwd: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(radius >= 0 && radius <= 4, "lookup_bwd: radius=%d not in [0,4]", radius);
+  RC_REQUIRE(valid_mode(coord_mode), "lookup_bwd: coord_mode=%d", coord_mode);
+  RC_REQUIRE(grad_levels || grad_coords, "lookup_bwd: nothing to compute");
+  if (grad_coords || !grad_levels)
+    if (int rc = check_levels(levels, num_levels, H, W, "lookup_bwd(levels)")) return rc;
+  if (grad_levels)
+    if (int rc = check_levels(grad_levels, num_levels, H, W, "lookup_bwd(grad_levels)")) return rc;
+  return launch_lookup_bwd(levels, grad_levels, num_levels, coords, grad_out, grad_coords, B, H, W,
+                           radius, coord_mode, (cudaStream_t)stream);
+}
+
+int64_t raftcorr_build_bwd_workspace_bytes(int B, int D, int H, int W) {
+  return build_bwd_workspace_bytes(B, D, H, W);
+}
+
+int raftcorr_build_bwd(const raftcorr_level* grad_levels, int num_levels, const float* fmap1,
+                       const float* fmap2, float* grad_fmap1, float* grad_fmap2, int B, int D,
+                       int H, int W, void* workspace, int64_t workspace_bytes, void* stream) {
+  RC_REQUIRE(fmap1 && fmap2 && grad_fmap1 && grad_fmap2, "build_bwd: NULL pointer");
+  RC_REQUIRE(B >= 0 && D >= 1 && H >= 1 && W >= 1, "build_bwd: bad sizes");
+  if (int rc = check_levels(grad_levels, num_levels, H, W, "build_bwd")) return rc;
+  return launch_build_bwd(grad_levels, num_levels, fmap1, fmap2, grad_fmap1, grad_fmap2, B, D, H, W,
+                          workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+int raftcorr_alt_fwd(const float* fmap1, const float* fmap2, const float* coords, float* corr,
+                     int B, int H1, int W1, int H2, int W2, int C, int radius, int coord_mode,
+                     float scale, void* stream) {
+  RC_REQUIRE(fmap1 && fmap2 && coords && corr, "alt_fwd: NULL pointer");
+  RC_REQUIRE(B >= 0 && H1 >= 1 && W1 >= 1 && H2 >= 1 && W2 >= 1 && C >= 1, "alt_fwd: bad sizes");
+  RC_REQUIRE(radius >= 0 && radius <= 4, "alt_fwd: radius=%d not in [0,4]", radius);
+  RC_REQUIRE(valid_mode(coord_mode), "alt_fwd: coord_mode=%d", coord_mode);
+  return launch_alt_fwd(fmap1, fmap2, coords, corr, B, H1, W1, H2, W2, C, radius, coord_mode, scale,
+                        (cudaStream_t)stream);
+}
+
+int raftcorr_alt_bwd(const float* fmap1, const float* fmap2, const float* coords,
+                     const float* corr_grad, float* fmap1_grad, float* fmap2_grad,
+                     float* coords_grad, int B, int H1, int W1, int H2, int W2, int C, int radius,
+                     int coord_mode, float scale, void* stream) {
+  RC_REQUIRE(fmap1 && fmap2 && coords && corr_grad && fmap1_grad && fmap2_grad,
+             "alt_bwd: NULL pointer");
+  RC_REQUIRE(B >= 0 && H1 >= 1 && W1 >= 1 && H2 >= 1 && W2 >= 1 && C >= 1, "alt_bwd: bad sizes");
+  RC_REQUIRE(radius >= 0 && radius <= 4, "alt_bwd: radius=%d not in [0,4]", radius);
+  RC_REQUIRE(valid_mode(coord_mode), "alt_bwd: coord_mode=%d", coord_mode);
+  return launch_alt_bwd(fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, coords_grad, B, H1,
+                        W1, H2, W2, C, radius, coord_mode, scale, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,137 @@
+// build_bwd.cu — backward of the volume build: d(pyramid) -> d(fmap1), d(fmap2).
+//
+// The reference gets this from autograd: AvgPool2DBackward0 x3 spreads each
+// pooled gradient over its 2x2 parents (/4), DivBackward0 applies 1/sqrt(D), BmmBackward0 forms
+//   d f1[b,d,i] = sum_j dC[b,i,j] f2[b,d,j]      d f2[b,d,j] = sum_i dC[b,i,j] f1[b,d,i].
+// Here the un-pool + scale is one pass that materialises dC in the caller's workspace, followed
+// by two fp32 FMA GEMMs (gradients are checked at rtol 1e-3, so they stay fp32).
+#include "common.cuh"
+
+namespace raftcorr {
+
+namespace {
+
+struct GradLevels {
+  const float* data[RAFTCORR_MAX_LEVELS];
+  int H[RAFTCORR_MAX_LEVELS], W[RAFTCORR_MAX_LEVELS];
+  long long pitch[RAFTCORR_MAX_LEVELS], istride[RAFTCORR_MAX_LEVELS];
+  int L;
+};
+
+// dC[q, j] = (1/sqrtD) * sum_l 4^-l * dP_l[q, jy>>l, jx>>l]   (levels that cover pixel j)
+__global__ void __launch_bounds__(256)
+unpool_kernel(const __grid_constant__ GradLevels g, float* __restrict__ dC, long long images, int H,
+              int W, float inv_sqrtD) {
+  const long long N = (long long)H * W;
+  const long long total = images * N;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const long long q = e / N;
+    const int j = (int)(e - q * N);
+    const int jy = j / W, jx = j - jy * W;
+    float acc = 0.0f, wgt = 1.0f;
+    for (int l = 0; l < g.L; ++l) {
+      const int yy = jy >> l, xx = jx >> l;
+      if (yy < g.H[l] && xx < g.W[l])
+        acc += wgt * __ldg(g.data[l] + q * g.istride[l] + (long long)yy * g.pitch[l] + xx);
+      wgt *= 0.25f;
+    }
+    dC[e] = acc * inv_sqrtD;
+  }
+}
+
+constexpr int kT = 64, kK = 16;
+
+// out[m, n] = sum_k A[m*a_m + k*a_k] * Bm[k*b_k + n*b_n]   (per batch), 64x64 tiles, 4x4 per thread
+__global__ void __launch_bounds__(256)
+sgemm_strided_kernel(const float* __restrict__ A, long long a_m, long long a_k, long long a_b,
+                     const float* __restrict__ Bm, long long b_k, long long b_n, long long b_b,
+                     float* __restrict__ out, long long o_m, long long o_b, int M, int Nn, int K) {
+  __shared__ float As[kK][kT + 1];
+  __shared__ float Bs[kK][kT + 1];
+  const int b = blockIdx.z;
+  A += b * a_b;
+  Bm += b * b_b;
+  out += b * o_b;
+  const int m0 = blockIdx.y * kT, n0 = blockIdx.x * kT;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < K; k0 += kK) {
+    for (int e = threadIdx.x; e < kK * kT; e += 256) {
+      // pick the faster-varying index so that unit-stride operands are read coalesced
+      int ka, ma, kb, nb;
+      if (a_k == 1) { ka = e % kK; ma = e / kK; } else { ma = e % kT; ka = e / kT; }
+      if (b_k == 1) { kb = e % kK; nb = e / kK; } else { nb = e % kT; kb = e / kT; }
+      As[ka][ma] = (k0 + ka < K && m0 + ma < M) ? __ldg(A + (m0 + ma) * a_m + (k0 + ka) * a_k) : 0.0f;
+      Bs[kb][nb] = (k0 + kb < K && n0 + nb < Nn) ? __ldg(Bm + (k0 + kb) * b_k + (n0 + nb) * b_n) : 0.0f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kK; ++k) {
+      float a[4], c[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        a[u] = As[k][ty * 4 + u];
+        c[u] = Bs[k][tx * 4 + u];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int w = 0; w < 4; ++w) acc[u][w] = fmaf(a[u], c[w], acc[u][w]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int m = m0 + ty * 4 + u;
+    if (m >= M) continue;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const int n = n0 + tx * 4 + w;
+      if (n < Nn) out[m * o_m + n] = acc[u][w];
+    }
+  }
+}
+
+}  // namespace
+
+int64_t build_bwd_workspace_bytes(int B, int D, int H, int W) {
+  (void)D;
+  const int64_t N = (int64_t)H * W;
+  return (int64_t)B * N * N * (int64_t)sizeof(float);
+}
+
+int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, const float* f2,
+                     float* g1, float* g2, int B, int D, int H, int W, void* ws, int64_t ws_bytes,
+                     cudaStream_t stream) {
+  const long long N = (long long)H * W;
+  if (B == 0) return 0;
+  if (ws == nullptr || ws_bytes < build_bwd_workspace_bytes(B, D, H, W))
+    return fail(RAFTCORR_E_WORKSPACE, "build_bwd: workspace %lld B < %lld B", (long long)ws_bytes,
+                (long long)build_bwd_workspace_bytes(B, D, H, W));
+  GradLevels g;
+  g.L = L;
+  for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
+    const int s = l < L ? l : 0;
+    g.data[l] = glevels[s].data;
+    g.H[l] = glevels[s].H;
+    g.W[l] = glevels[s].W;
+    g.pitch[l] = glevels[s].pitch;
+    g.istride[l] = glevels[s].image_stride;
+  }
+  float* dC = static_cast<float*>(ws);
+  unpool_kernel<<<148 * 8, 256, 0, stream>>>(g, dC, (long long)B * N, H, W, 1.0f / sqrtf((float)D));
+  RC_CHECK_CUDA(cudaGetLastError());
+  dim3 grid((unsigned)((N + kT - 1) / kT), (unsigned)((D + kT - 1) / kT), (unsigned)B);
+  // d f1[d, i] = sum_j f2[d, j] * dC[i, j]
+  sgemm_strided_kernel<<<grid, 256, 0, stream>>>(f2, N, 1, (long long)D * N, dC, 1, N, N * N, g1, N,
+                                                 (long long)D * N, D, (int)N, (int)N);
+  RC_CHECK_CUDA(cudaGetLastError());
+  // d f2[d, j] = sum_i f1[d, i] * dC[i, j]
+  sgemm_strided_kernel<<<grid, 256, 0, stream>>>(f1, N, 1, (long long)D * N, dC, N, 1, N * N, g2, N,
+                                                 (long long)D * N, D, (int)N, (int)N);
+  RC_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace raftcorr

@@ -1,0 +1,514 @@
+// build_tc.cu — all-pairs volume + 4-level pyramid on the 5th-gen tensor cores (kernel family 1).
+//
+// Replaces CorrBlock.corr + the avg_pool2d chain (reference core/corr.py:21-27, 52-60):
+//   C[b, i, j] = <fmap1[b,:,i], fmap2[b,:,j]> / sqrt(D), then three 2x2 means.
+// The reference materialises C with cuBLAS, re-reads it for the division and re-reads it again
+// for every pooling level.  Here a persistent, warp-specialised tcgen05 GEMM keeps the 128 x 256
+// accumulator tile in TMEM; the N side of a tile is a 2-D block of 8 x 32 target pixels, so one
+// TMEM lane (= one query) holds a whole 8x32 patch and the epilogue scales it, forms the 4x16,
+// 2x8 and 1x4 pooled patches in registers and writes all four levels once, through swizzled
+// shared-memory staging and TMA tensor stores (which also clip ragged edges).
+//
+//   warp 0      TMA producer   (A: 128 queries x 128 B of K;  B: 8x32 pixels x 128 B of K)
+//   warp 1      MMA issuer     (tcgen05.mma cta_group::1, kind::f16 / kind::tf32, M128 N256)
+//   warps 2-5   epilogue group 0 (accumulator stage 0)     warps 6-9   epilogue group 1
+//
+// Operands come from pack_kernel: NCHW fp32 -> (B, N, D) K-major bf16 (or tf32-rounded fp32).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace raftcorr {
+
+namespace {
+
+constexpr int kBlockM = 128;             // queries per tile  (TMEM lanes)
+constexpr int kTileY = 8, kTileX = 32;   // target-pixel block per tile
+constexpr int kBlockN = kTileY * kTileX; // 256 TMEM columns
+constexpr int kStages = 3;
+constexpr int kBytesA = kBlockM * 128;   // 16 KB per k-block (128 B of K per row)
+constexpr int kBytesB = kBlockN * 128;   // 32 KB
+constexpr int kStageBytes = kBytesA + kBytesB;
+constexpr int kEpiWarps = 8;
+constexpr int kEpiBufBytes = 4096;       // one staged row: 32 queries x 128 B
+constexpr int kSmemStaging = kStages * kStageBytes;
+constexpr int kSmemBars = kSmemStaging + kEpiWarps * 2 * kEpiBufBytes;
+constexpr int kSmemTotal = kSmemBars + 128;
+constexpr int kThreads = 32 * (2 + kEpiWarps);
+
+struct BuildTcParams {
+  int B, N, H, W, L;
+  int tiles_m, tiles_y, tiles_x;
+  int k_blocks;       // ceil(D * elem_size / 128)
+  int k_elems;        // K elements per 128 B
+  uint32_t idesc;
+  float inv_scale;    // 1 / sqrt(D)
+  int Hl[RAFTCORR_MAX_LEVELS], Wl[RAFTCORR_MAX_LEVELS];
+};
+
+// ---- PTX wrappers --------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded wait: a protocol bug must surface as a launch failure, never as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  const long long t0 = clock64();
+  uint32_t done = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) return;
+    if (clock64() - t0 > 8000000000LL) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0,
+                                            int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0,
+                                            int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2,
+                                             int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+template <bool kTf32>
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                       uint32_t accumulate) {
+  if constexpr (kTf32) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+// 32 lanes x 64 consecutive fp32 columns -> 64 registers per thread
+__device__ __forceinline__ void tmem_ld_x64(uint32_t taddr, float* f) {
+  uint32_t* v = reinterpret_cast<uint32_t*>(f);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x64.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, "
+      "%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, "
+      "%48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]),
+        "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]),
+        "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]),
+        "=r"(v[29]), "=r"(v[30]), "=r"(v[31]), "=r"(v[32]), "=r"(v[33]), "=r"(v[34]), "=r"(v[35]),
+        "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]), "=r"(v[40]), "=r"(v[41]), "=r"(v[42]),
+        "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]), "=r"(v[49]),
+        "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]),
+        "=r"(v[57]), "=r"(v[58]), "=r"(v[59]), "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, 128-byte swizzle: rows of 128 B, 8-row groups 1024 B apart (SBO), version 1.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;            // leading byte offset (unused with swizzle): 1
+  d |= (uint64_t)(1024 >> 4) << 32;  // stride byte offset
+  d |= (uint64_t)1 << 46;            // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;            // SWIZZLE_128B
+  return d;
+}
+
+// Stage one row segment (kNF floats per query, 32 queries) in swizzled shared memory and hand it
+// to the TMA store engine.  slot alternates between the warp's two 4 KB buffers.
+template <int kNF>
+__device__ __forceinline__ void stage_and_store(const float* vals, const CUtensorMap* map, uint32_t buf_base,
+                                                uint32_t& nstores, int lane, int X0, int Y, int q0, int b) {
+  const uint32_t buf = buf_base + (nstores & 1) * kEpiBufBytes;
+  ++nstores;
+  if (lane == 0) bulk_wait_read<1>();  // the store issued two rows ago has drained this buffer
+  __syncwarp();
+  constexpr int kChunks = kNF / 4;
+#pragma unroll
+  for (int c = 0; c < kChunks; ++c) {
+    int phys = c;
+    if (kNF == 32) phys = c ^ (lane & 7);          // SWIZZLE_128B
+    if (kNF == 16) phys = c ^ ((lane >> 1) & 3);   // SWIZZLE_64B
+    if (kNF == 8) phys = c ^ ((lane >> 2) & 1);    // SWIZZLE_32B
+    const uint32_t addr = buf + lane * (kNF * 4) + phys * 16;
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(vals[4 * c]),
+                 "f"(vals[4 * c + 1]), "f"(vals[4 * c + 2]), "f"(vals[4 * c + 3])
+                 : "memory");
+  }
+  fence_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_4d(map, buf, X0, Y, q0, b);
+    bulk_commit();
+  }
+}
+
+template <bool kTf32>
+__global__ void __launch_bounds__(kThreads, 1)
+build_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+                const __grid_constant__ CUtensorMap mapL0, const __grid_constant__ CUtensorMap mapL1,
+                const __grid_constant__ CUtensorMap mapL2, const __grid_constant__ CUtensorMap mapL3,
+                const __grid_constant__ BuildTcParams p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t bars = smem_base + kSmemBars;
+  // barrier slots (8 B each): full[3] empty[3] tmem_full[2] tmem_empty[2]; then the TMEM address
+  auto full_bar = [&](int s) { return bars + 8 * s; };
+  auto empty_bar = [&](int s) { return bars + 8 * (kStages + s); };
+  auto tfull_bar = [&](int a) { return bars + 8 * (2 * kStages + a); };
+  auto tempty_bar = [&](int a) { return bars + 8 * (2 * kStages + 2 + a); };
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kSmemBars + 8 * (2 * kStages + 4));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
+                     smem_u32(const_cast<uint32_t*>(tmem_slot)))
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const long long tiles_n = (long long)p.tiles_y * p.tiles_x;
+  const long long total = (long long)p.B * p.tiles_m * tiles_n;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (long long t = blockIdx.x; t < total; t += gridDim.x) {
+        const int nt = (int)(t % tiles_n);
+        const int mt = (int)((t / tiles_n) % p.tiles_m);
+        const int b = (int)(t / (tiles_n * p.tiles_m));
+        const int ty = nt / p.tiles_x, tx = nt - ty * p.tiles_x;
+        for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t ph = (it / kStages) & 1;
+          mbar_wait(empty_bar(s), ph ^ 1);
+          mbar_expect_tx(full_bar(s), kStageBytes);
+          const uint32_t a_dst = smem_base + s * kStageBytes;
+          tma_load_3d(a_dst, &mapA, full_bar(s), kb * p.k_elems, mt * kBlockM, b);
+          tma_load_4d(a_dst + kBytesA, &mapB, full_bar(s), kb * p.k_elems, tx * kTileX, ty * kTileY, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      uint32_t it = 0, i = 0;
+      for (long long t = blockIdx.x; t < total; t += gridDim.x, ++i) {
+        const int as = i & 1;
+        const uint32_t aph = (i >> 1) & 1;
+        mbar_wait(tempty_bar(as), aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * kBlockN;
+        for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t ph = (it / kStages) & 1;
+          mbar_wait(full_bar(s), ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_base + s * kStageBytes;
+          const uint64_t adesc = make_smem_desc(a_addr);
+          const uint64_t bdesc = make_smem_desc(a_addr + kBytesA);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)  // 4 x 32 B of K per 128 B row; +2 in the 16-byte address field
+            tc_mma<kTf32>(d_tmem, adesc + 2 * k, bdesc + 2 * k, p.idesc, (kb | k) != 0);
+          tc_commit(empty_bar(s));
+        }
+        tc_commit(tfull_bar(as));
+      }
+    }
+  } else {
+    const int ew = warp - 2;          // 0..7
+    const int group = ew >> 2;        // accumulator stage this warp drains
+    const int quarter = warp & 3;     // TMEM lanes 32*quarter .. +31 are visible to this warp
+    const uint32_t buf_base = smem_base + kSmemStaging + ew * 2 * kEpiBufBytes;
+    uint32_t nstores = 0, i = 0;
+    for (long long t = blockIdx.x; t < total; t += gridDim.x, ++i) {
+      if ((int)(i & 1) != group) continue;
+      const uint32_t aph = (i >> 1) & 1;
+      const int nt = (int)(t % tiles_n);
+      const int mt = (int)((t / tiles_n) % p.tiles_m);
+      const int b = (int)(t / (tiles_n * p.tiles_m));
+      const int ty = nt / p.tiles_x, tx = nt - ty * p.tiles_x;
+      const int y0 = ty * kTileY, x0 = tx * kTileX;
+      const int q0 = mt * kBlockM + quarter * 32;
+      const bool rows_live = q0 < p.N;
+      mbar_wait(tfull_bar(group), aph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + group * kBlockN;
+      float p1[2][16];
+      float p2[2][8];
+#pragma unroll
+      for (int rp = 0; rp < 4; ++rp) {
+        float f[64];
+        tmem_ld_x64(taddr + rp * 64, f);
+        tmem_ld_wait();
+        if (rp == 3) {  // accumulator fully read: hand the TMEM stage back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(group));
+        }
+        if (!rows_live) continue;
+#pragma unroll
+        for (int c = 0; c < 64; ++c) f[c] *= p.inv_scale;  // corr.py:60
+        if (y0 + 2 * rp < p.H) stage_and_store<32>(f, &mapL0, buf_base, nstores, lane, x0, y0 + 2 * rp, q0, b);
+        if (y0 + 2 * rp + 1 < p.H)
+          stage_and_store<32>(f + 32, &mapL0, buf_base, nstores, lane, x0, y0 + 2 * rp + 1, q0, b);
+        // 2x2 means in ATen's order ((a+b)+c)+d, then /4 (corr.py:26)
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          p1[rp & 1][k] = (((f[2 * k] + f[2 * k + 1]) + f[32 + 2 * k]) + f[33 + 2 * k]) * 0.25f;
+        if (p.L > 1 && (y0 >> 1) + rp < p.Hl[1] && (x0 >> 1) < p.Wl[1])
+          stage_and_store<16>(p1[rp & 1], &mapL1, buf_base, nstores, lane, x0 >> 1, (y0 >> 1) + rp, q0, b);
+        if (rp & 1) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            p2[rp >> 1][k] =
+                (((p1[0][2 * k] + p1[0][2 * k + 1]) + p1[1][2 * k]) + p1[1][2 * k + 1]) * 0.25f;
+          if (p.L > 2 && (y0 >> 2) + (rp >> 1) < p.Hl[2] && (x0 >> 2) < p.Wl[2])
+            stage_and_store<8>(p2[rp >> 1], &mapL2, buf_base, nstores, lane, x0 >> 2, (y0 >> 2) + (rp >> 1), q0, b);
+        }
+      }
+      if (rows_live && p.L > 3 && (y0 >> 3) < p.Hl[3] && (x0 >> 3) < p.Wl[3]) {
+        float p3[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          p3[k] = (((p2[0][2 * k] + p2[0][2 * k + 1]) + p2[1][2 * k]) + p2[1][2 * k + 1]) * 0.25f;
+        stage_and_store<4>(p3, &mapL3, buf_base, nstores, lane, x0 >> 3, y0 >> 3, q0, b);
+      }
+    }
+    if (lane == 0) bulk_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+  }
+}
+
+// NCHW fp32 (B, D, N) -> K-major (B, N, D): bf16, or fp32 rounded to tf32 (cvt.rna)
+template <typename T>
+__global__ void __launch_bounds__(256)
+pack_kernel(const float* __restrict__ src, T* __restrict__ dst, int D, int N) {
+  __shared__ float tile[64][33];
+  const int b = blockIdx.z;
+  const int n0 = blockIdx.x * 32, d0 = blockIdx.y * 64;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const float* s = src + (long long)b * D * N;
+  for (int c = w; c < 64; c += 8) {
+    const int d = d0 + c, n = n0 + lane;
+    tile[c][lane] = (d < D && n < N) ? __ldg(s + (long long)d * N + n) : 0.0f;
+  }
+  __syncthreads();
+  T* o = dst + (long long)b * N * D;
+  for (int px = w; px < 32; px += 8) {
+    const int n = n0 + px;
+    const int d = d0 + 2 * lane;
+    if (n >= N || d >= D) continue;  // D is even (checked by the launcher)
+    const float v0 = tile[2 * lane][px], v1 = tile[2 * lane + 1][px];
+    if constexpr (sizeof(T) == 2) {
+      *reinterpret_cast<__nv_bfloat162*>(o + (long long)n * D + d) = __floats2bfloat162_rn(v0, v1);
+    } else {
+      uint32_t r0, r1;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r0) : "f"(v0));
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r1) : "f"(v1));
+      *reinterpret_cast<float2*>(o + (long long)n * D + d) = make_float2(__uint_as_float(r0), __uint_as_float(r1));
+    }
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+int encode(CUtensorMap* m, CUtensorMapDataType dt, int rank, void* base, const cuuint64_t* dims,
+           const cuuint64_t* strides, const cuuint32_t* box, CUtensorMapSwizzle sw, const char* what) {
+  EncodeTiledFn fn = get_encode();
+  if (!fn) return fail(RAFTCORR_E_DRIVER, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint32_t ones[5] = {1, 1, 1, 1, 1};
+  const CUresult r = fn(m, dt, (cuuint32_t)rank, base, dims, strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(RAFTCORR_E_INVALID, "cuTensorMapEncodeTiled(%s) failed: CUresult %d", what, (int)r);
+  return 0;
+}
+
+size_t elem_size(int precision) { return precision == RAFTCORR_PREC_BF16 ? 2 : 4; }
+
+int64_t align256(int64_t v) { return (v + 255) & ~(int64_t)255; }
+
+}  // namespace
+
+int64_t build_tc_workspace_bytes(int B, int D, int H, int W, int precision) {
+  return 2 * align256((int64_t)B * H * W * D * (int64_t)elem_size(precision));
+}
+
+int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W, int L,
+                    const raftcorr_level* levels, int precision, void* ws, int64_t ws_bytes,
+                    cudaStream_t stream) {
+  const int N = H * W;
+  if (B == 0) return 0;
+  const size_t es = elem_size(precision);
+  if (D % 8 != 0) return fail(RAFTCORR_E_UNSUPPORTED, "build_pyramid: tensor-core path needs D %% 8 == 0 (D=%d)", D);
+  if (ws == nullptr || ws_bytes < build_tc_workspace_bytes(B, D, H, W, precision) ||
+      (reinterpret_cast<uintptr_t>(ws) & 255))
+    return fail(RAFTCORR_E_WORKSPACE, "build_pyramid: workspace must be 256-byte aligned and >= %lld B",
+                (long long)build_tc_workspace_bytes(B, D, H, W, precision));
+  for (int l = 0; l < L; ++l)
+    if ((levels[l].pitch & 3) || (levels[l].image_stride & 3) ||
+        (reinterpret_cast<uintptr_t>(levels[l].data) & 15))
+      return fail(RAFTCORR_E_UNSUPPORTED,
+                  "build_pyramid: level %d needs 16-byte aligned rows (pitch %% 4 == 0; use raftcorr_pyramid_layout)", l);
+
+  char* wsb = static_cast<char*>(ws);
+  void* packA = wsb;
+  void* packB = wsb + align256((int64_t)B * N * D * (int64_t)es);
+  dim3 pgrid((N + 31) / 32, (D + 63) / 64, B);
+  if (precision == RAFTCORR_PREC_BF16) {
+    pack_kernel<__nv_bfloat16><<<pgrid, 256, 0, stream>>>(f1, static_cast<__nv_bfloat16*>(packA), D, N);
+    pack_kernel<__nv_bfloat16><<<pgrid, 256, 0, stream>>>(f2, static_cast<__nv_bfloat16*>(packB), D, N);
+  } else {
+    pack_kernel<float><<<pgrid, 256, 0, stream>>>(f1, static_cast<float*>(packA), D, N);
+    pack_kernel<float><<<pgrid, 256, 0, stream>>>(f2, static_cast<float*>(packB), D, N);
+  }
+  RC_CHECK_CUDA(cudaGetLastError());
+
+  const CUtensorMapDataType dt =
+      precision == RAFTCORR_PREC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  const cuuint32_t k_elems = (cuuint32_t)(128 / es);
+  CUtensorMap mapA, mapB, mapL[RAFTCORR_MAX_LEVELS];
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)B};
+    cuuint64_t strides[2] = {(cuuint64_t)D * es, (cuuint64_t)N * D * es};
+    cuuint32_t box[3] = {k_elems, kBlockM, 1};
+    if (int rc = encode(&mapA, dt, 3, packA, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "A")) return rc;
+  }
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)D * es, (cuuint64_t)W * D * es, (cuuint64_t)N * D * es};
+    cuuint32_t box[4] = {k_elems, kTileX, kTileY, 1};
+    if (int rc = encode(&mapB, dt, 4, packB, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "B")) return rc;
+  }
+  const CUtensorMapSwizzle sw[4] = {CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_SWIZZLE_64B,
+                                    CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_NONE};
+  for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
+    const raftcorr_level& lv = levels[l < L ? l : 0];
+    cuuint64_t dims[4] = {(cuuint64_t)lv.W, (cuuint64_t)lv.H, (cuuint64_t)N, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)lv.pitch * 4, (cuuint64_t)lv.image_stride * 4,
+                             (cuuint64_t)lv.image_stride * 4 * N};
+    const int sl = l < L ? l : 0;
+    cuuint32_t box[4] = {(cuuint32_t)(kTileX >> sl), 1, 32, 1};
+    if (int rc = encode(&mapL[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, lv.data, dims, strides, box, sw[sl], "level"))
+      return rc;
+  }
+
+  BuildTcParams p;
+  p.B = B;
+  p.N = N;
+  p.H = H;
+  p.W = W;
+  p.L = L;
+  p.tiles_m = (N + kBlockM - 1) / kBlockM;
+  p.tiles_y = (H + kTileY - 1) / kTileY;
+  p.tiles_x = (W + kTileX - 1) / kTileX;
+  p.k_elems = (int)k_elems;
+  p.k_blocks = (int)((D + k_elems - 1) / k_elems);
+  const uint32_t fmt = precision == RAFTCORR_PREC_BF16 ? 1u : 2u;
+  p.idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(kBlockN >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+  p.inv_scale = 1.0f / sqrtf((float)D);
+  for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
+    p.Hl[l] = H >> l;
+    p.Wl[l] = W >> l;
+  }
+  int dev = 0, sms = 0;
+  RC_CHECK_CUDA(cudaGetDevice(&dev));
+  RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const long long total = (long long)B * p.tiles_m * p.tiles_y * p.tiles_x;
+  const int grid = (int)(total < sms ? total : sms);
+  if (precision == RAFTCORR_PREC_BF16) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<false><<<grid, kThreads, kSmemTotal, stream>>>(mapA, mapB, mapL[0], mapL[1], mapL[2], mapL[3], p);
+  } else {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<true><<<grid, kThreads, kSmemTotal, stream>>>(mapA, mapB, mapL[0], mapL[1], mapL[2], mapL[3], p);
+  }
+  RC_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace raftcorr

@@ -1,0 +1,256 @@
+"""torch-facing wrappers over the C ABI: tensors in, tensors out, current device + stream.
+
+PyTorch is plumbing here (device memory, streams, autograd bookkeeping); all arithmetic of the
+correlation path runs in libraftcorr_b200.so.  Nothing in this file computes on the CPU or
+falls back to ATen ops.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _capi
+from ._capi import (COORD_ATEN_CPU, COORD_ATEN_CUDA, COORD_DIRECT, PREC_BF16, PREC_FP32, PREC_TF32,
+                    Level, LevelArray)
+
+_PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "tf32": PREC_TF32}
+_COORD_MODES = {"aten_cpu": COORD_ATEN_CPU, "aten_cuda": COORD_ATEN_CUDA, "direct": COORD_DIRECT}
+
+
+def resolve_precision(precision) -> int:
+    """'bf16' (default; one tcgen05 pass, 5e-4 px EPE drift on RAFT), 'tf32' or 'fp32'."""
+    if precision is None:
+        precision = os.environ.get("RAFTCORR_PRECISION", "bf16")
+    if isinstance(precision, str):
+        if precision not in _PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(_PRECISIONS)}, got {precision!r}")
+        return _PRECISIONS[precision]
+    return int(precision)
+
+
+def resolve_coord_mode(mode) -> int:
+    if mode is None:
+        mode = os.environ.get("RAFTCORR_COORD_MODE", "aten_cpu")
+    if isinstance(mode, str):
+        if mode not in _COORD_MODES:
+            raise ValueError(f"coord_mode must be one of {sorted(_COORD_MODES)}, got {mode!r}")
+        return _COORD_MODES[mode]
+    return int(mode)
+
+
+def _stream(t: torch.Tensor) -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _require_cuda_f32(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+
+
+class Pyramid:
+    """Device storage of a correlation pyramid (core/corr.py:21-27's ``corr_pyramid``) with rows
+    padded to 16 bytes, plus the raftcorr_level descriptors that describe it to the kernels."""
+
+    def __init__(self, B: int, H: int, W: int, num_levels: int, device, zero: bool = False):
+        self.B, self.H, self.W, self.num_levels = B, H, W, num_levels
+        self.desc = LevelArray()
+        floats = (ctypes.c_int64 * _capi.MAX_LEVELS)()
+        _capi.check(_capi.lib().raftcorr_pyramid_layout(B, H, W, num_levels, self.desc, floats),
+                    "raftcorr_pyramid_layout")
+        alloc = torch.zeros if zero else torch.empty
+        self.storage: List[torch.Tensor] = []
+        for l in range(num_levels):
+            d = self.desc[l]
+            buf = alloc((B * H * W, d.H, d.pitch), dtype=torch.float32, device=device)
+            d.data = buf.data_ptr()
+            self.storage.append(buf)
+
+    def views(self) -> List[torch.Tensor]:
+        """(B*H*W, 1, H_l, W_l) strided views, the shape core/corr.py:22-27 exposes."""
+        return [self.storage[l][:, :, : self.desc[l].W].unsqueeze(1) for l in range(self.num_levels)]
+
+
+def build_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
+                  precision=None) -> Pyramid:
+    """core/corr.py:13-27 + 52-60 in one launch sequence (pack, tcgen05 GEMM + pooled epilogue)."""
+    _require_cuda_f32(fmap1, "fmap1")
+    _require_cuda_f32(fmap2, "fmap2")
+    if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
+        raise RuntimeError(f"fmap1/fmap2 must both be (B,D,H,W); got {tuple(fmap1.shape)} and {tuple(fmap2.shape)}")
+    fmap1, fmap2 = fmap1.contiguous(), fmap2.contiguous()
+    B, D, H, W = fmap1.shape
+    prec = resolve_precision(precision)
+    lib = _capi.lib()
+    with torch.cuda.device(fmap1.device):
+        pyr = Pyramid(B, H, W, num_levels, fmap1.device)
+        ws_bytes = int(lib.raftcorr_build_workspace_bytes(B, D, H, W, prec))
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=fmap1.device)
+        _capi.check(lib.raftcorr_build_pyramid(fmap1.data_ptr(), fmap2.data_ptr(), B, D, H, W, num_levels,
+                                               pyr.desc, prec, ws.data_ptr(), ws_bytes, _stream(fmap1)),
+                    "raftcorr_build_pyramid")
+        ws.record_stream(torch.cuda.current_stream(fmap1.device))
+    return pyr
+
+
+def lookup(pyr: Pyramid, coords: torch.Tensor, radius: int, coord_mode=None) -> torch.Tensor:
+    """core/corr.py:29-50: coords (B,2,H,W) -> (B, L*(2r+1)^2, H, W) fp32 contiguous."""
+    _require_cuda_f32(coords, "coords")
+    B, two, H, W = coords.shape
+    if two != 2 or (B, H, W) != (pyr.B, pyr.H, pyr.W):
+        raise RuntimeError(f"coords must be ({pyr.B},2,{pyr.H},{pyr.W}); got {tuple(coords.shape)}")
+    coords = coords.contiguous()
+    rd = 2 * radius + 1
+    out = torch.empty((B, pyr.num_levels * rd * rd, H, W), dtype=torch.float32, device=coords.device)
+    with torch.cuda.device(coords.device):
+        _capi.check(_capi.lib().raftcorr_lookup_fwd(pyr.desc, pyr.num_levels, coords.data_ptr(), out.data_ptr(),
+                                                    B, H, W, radius, resolve_coord_mode(coord_mode),
+                                                    _stream(coords)), "raftcorr_lookup_fwd")
+    return out
+
+
+def lookup_backward(pyr: Optional[Pyramid], grad_pyr: Optional[Pyramid], coords: torch.Tensor,
+                    grad_out: torch.Tensor, radius: int, want_coords: bool, coord_mode=None):
+    """Scatter grad_out into grad_pyr (accumulating) and/or return d coords."""
+    coords = coords.contiguous()
+    grad_out = grad_out.contiguous()
+    B, _, H, W = coords.shape
+    gcoords = torch.empty_like(coords) if want_coords else None
+    ref = grad_pyr if grad_pyr is not None else pyr
+    with torch.cuda.device(coords.device):
+        _capi.check(_capi.lib().raftcorr_lookup_bwd(
+            pyr.desc if pyr is not None else None, grad_pyr.desc if grad_pyr is not None else None,
+            ref.num_levels, coords.data_ptr(), grad_out.data_ptr(),
+            gcoords.data_ptr() if want_coords else None, B, H, W, radius,
+            resolve_coord_mode(coord_mode), _stream(coords)), "raftcorr_lookup_bwd")
+    return gcoords
+
+
+def build_backward(grad_pyr: Pyramid, fmap1: torch.Tensor, fmap2: torch.Tensor):
+    fmap1, fmap2 = fmap1.contiguous(), fmap2.contiguous()
+    B, D, H, W = fmap1.shape
+    lib = _capi.lib()
+    g1, g2 = torch.empty_like(fmap1), torch.empty_like(fmap2)
+    with torch.cuda.device(fmap1.device):
+        ws_bytes = int(lib.raftcorr_build_bwd_workspace_bytes(B, D, H, W))
+        ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=fmap1.device)
+        _capi.check(lib.raftcorr_build_bwd(grad_pyr.desc, grad_pyr.num_levels, fmap1.data_ptr(), fmap2.data_ptr(),
+                                           g1.data_ptr(), g2.data_ptr(), B, D, H, W, ws.data_ptr(), ws_bytes,
+                                           _stream(fmap1)), "raftcorr_build_bwd")
+        ws.record_stream(torch.cuda.current_stream(fmap1.device))
+    return g1, g2
+
+
+def alt_forward(fmap1: torch.Tensor, fmap2: torch.Tensor, coords: torch.Tensor, radius: int,
+                coord_mode=COORD_DIRECT, scale: float = 1.0) -> torch.Tensor:
+    """alt_cuda_corr.forward layouts: fmap1 (B,H1,W1,C), fmap2 (B,H2,W2,C), coords (B,1,H1,W1,2)."""
+    B, H1, W1, C = fmap1.shape
+    _, H2, W2, _ = fmap2.shape
+    rd = 2 * radius + 1
+    corr = torch.empty((B, 1, rd * rd, H1, W1), dtype=torch.float32, device=fmap1.device)
+    with torch.cuda.device(fmap1.device):
+        _capi.check(_capi.lib().raftcorr_alt_fwd(fmap1.data_ptr(), fmap2.data_ptr(), coords.data_ptr(),
+                                                 corr.data_ptr(), B, H1, W1, H2, W2, C, radius,
+                                                 resolve_coord_mode(coord_mode), scale, _stream(fmap1)),
+                    "raftcorr_alt_fwd")
+    return corr
+
+
+def alt_backward(fmap1, fmap2, coords, corr_grad, radius: int, coord_mode=COORD_DIRECT,
+                 scale: float = 1.0, want_coords: bool = True):
+    B, H1, W1, C = fmap1.shape
+    _, H2, W2, _ = fmap2.shape
+    g1, g2 = torch.zeros_like(fmap1), torch.zeros_like(fmap2)
+    gc = torch.empty_like(coords) if want_coords else None
+    with torch.cuda.device(fmap1.device):
+        _capi.check(_capi.lib().raftcorr_alt_bwd(fmap1.data_ptr(), fmap2.data_ptr(), coords.data_ptr(),
+                                                 corr_grad.data_ptr(), g1.data_ptr(), g2.data_ptr(),
+                                                 gc.data_ptr() if want_coords else None, B, H1, W1, H2, W2,
+                                                 C, radius, resolve_coord_mode(coord_mode), scale,
+                                                 _stream(fmap1)), "raftcorr_alt_bwd")
+    return g1, g2, gc
+
+
+# ---- autograd -------------------------------------------------------------------------------
+class _GradSink:
+    """Shared d(pyramid) accumulator: every lookup of one CorrBlock scatters into the same
+    buffers instead of materialising a volume-sized gradient per iteration."""
+
+    def __init__(self):
+        self.grad_pyr: Optional[Pyramid] = None
+
+    def buffers(self, like: Pyramid, device) -> Pyramid:
+        if self.grad_pyr is None:
+            self.grad_pyr = Pyramid(like.B, like.H, like.W, like.num_levels, device, zero=True)
+        return self.grad_pyr
+
+
+class BuildFn(torch.autograd.Function):
+    """fmaps -> (token, level views).  The 1-element token is fed to every LookupFn so that
+    autograd runs this node's backward only after all lookups have scattered their gradients."""
+
+    @staticmethod
+    def forward(ctx, fmap1, fmap2, num_levels, precision, holder):
+        pyr = build_pyramid(fmap1, fmap2, num_levels, precision)
+        holder["pyr"] = pyr
+        holder["sink"] = _GradSink()
+        ctx.holder = holder
+        ctx.save_for_backward(fmap1, fmap2)
+        token = torch.zeros(1, dtype=torch.float32, device=fmap1.device)
+        return (token, *pyr.views())
+
+    @staticmethod
+    def backward(ctx, gtoken, *glevels):
+        fmap1, fmap2 = ctx.saved_tensors
+        pyr: Pyramid = ctx.holder["pyr"]
+        sink: _GradSink = ctx.holder["sink"]
+        gp = sink.buffers(pyr, fmap1.device)
+        for l, g in enumerate(glevels):  # gradients that reached corr_pyramid[l] directly
+            if g is not None:
+                gp.storage[l][:, :, : gp.desc[l].W].add_(g.squeeze(1))
+        g1, g2 = build_backward(gp, fmap1, fmap2)
+        sink.grad_pyr = None
+        return g1, g2, None, None, None
+
+
+class LookupFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, coords, token, holder, radius, coord_mode):
+        ctx.holder, ctx.radius, ctx.coord_mode = holder, radius, coord_mode
+        ctx.save_for_backward(coords)
+        return lookup(holder["pyr"], coords, radius, coord_mode)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (coords,) = ctx.saved_tensors
+        pyr: Pyramid = ctx.holder["pyr"]
+        want_levels = ctx.needs_input_grad[1]
+        want_coords = ctx.needs_input_grad[0]
+        gp = ctx.holder["sink"].buffers(pyr, coords.device) if want_levels else None
+        gcoords = None
+        if want_levels or want_coords:
+            gcoords = lookup_backward(pyr if want_coords else None, gp, coords, grad_out, ctx.radius,
+                                      want_coords, ctx.coord_mode)
+        gtoken = torch.zeros(1, dtype=torch.float32, device=coords.device) if want_levels else None
+        return gcoords, gtoken, None, None, None
+
+
+class AltFn(torch.autograd.Function):
+    """One level of the on-the-fly path with alt_cuda_corr's layouts, differentiable."""
+
+    @staticmethod
+    def forward(ctx, fmap1, fmap2, coords, radius, coord_mode, scale):
+        ctx.radius, ctx.coord_mode, ctx.scale = radius, coord_mode, scale
+        ctx.save_for_backward(fmap1, fmap2, coords)
+        return alt_forward(fmap1, fmap2, coords, radius, coord_mode, scale)
+
+    @staticmethod
+    def backward(ctx, grad):
+        fmap1, fmap2, coords = ctx.saved_tensors
+        g1, g2, gc = alt_backward(fmap1, fmap2, coords, grad.contiguous(), ctx.radius, ctx.coord_mode,
+                                  ctx.scale, want_coords=ctx.needs_input_grad[2])
+        return g1, g2, gc, None, None, None

@@ -1,0 +1,140 @@
+"""The drop-in classes end to end (build + lookup), forward and backward, against the golden
+vectors produced by the reference CorrBlock and its autograd."""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from oracle import torch_restatement as tr
+from helpers import rel_max
+
+warnings.filterwarnings("ignore")
+pytestmark = pytest.mark.gpu
+
+
+def _t(a, grad=False):
+    return torch.from_numpy(np.array(a)).cuda().requires_grad_(grad)
+
+
+@pytest.mark.parametrize("kind", ("grid", "half", "sigma4", "sigma30"))
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-5), ("tf32", 1e-2), ("bf16", 1e-2)])
+def test_corrblock_forward_golden(golden, kind, precision, tol):
+    import corr
+    g = golden("corr_tiny")
+    with torch.no_grad():
+        blk = corr.CorrBlock(_t(g["fmap1"]), _t(g["fmap2"]), num_levels=4, radius=4, precision=precision)
+        out = blk(_t(g[f"coords_{kind}"]))
+    assert blk.num_levels == 4 and blk.radius == 4
+    assert [tuple(p.shape) for p in blk.corr_pyramid] == [(288, 1, 16, 18), (288, 1, 8, 9), (288, 1, 4, 4), (288, 1, 2, 2)]
+    ref = g[f"out_{kind}"]
+    assert out.shape == ref.shape and out.is_contiguous() and out.dtype == torch.float32
+    o = out.cpu().numpy()
+    assert np.array_equal(o == 0, ref == 0)        # indexing / zero-padding masks: exact
+    assert rel_max(o, ref) <= tol
+
+
+def test_corrblock_backward_golden(golden):
+    """d fmap1, d fmap2, d coords vs the reference's autograd.
+    Atomics make the sums order-dependent: allclose(rtol 1e-3, atol 1e-4 max)."""
+    import corr
+    g = golden("corr_tiny")
+    f1, f2, c = _t(g["fmap1"], True), _t(g["fmap2"], True), _t(g["coords_sigma4"], True)
+    blk = corr.CorrBlock(f1, f2, precision="fp32")
+    out = blk(c)
+    assert rel_max(out.detach().cpu().numpy(), g["out_sigma4"]) <= 1e-5
+    out.backward(_t(g["grad_out"]))
+    for got, key in ((f1.grad, "grad_fmap1"), (f2.grad, "grad_fmap2"), (c.grad, "grad_coords")):
+        ref = g[key]
+        assert got is not None, key
+        assert np.allclose(got.cpu().numpy(), ref, rtol=1e-3, atol=1e-4 * np.abs(ref).max()), key
+
+
+def test_twelve_lookups_share_one_gradient_buffer(golden):
+    """RAFT's training graph: one build, many lookups with detached coords (raft.py:122-124).
+    The gradient of a sum over lookups must equal the reference autograd's."""
+    import corr
+    g = golden("corr_tiny")
+    gen = torch.Generator().manual_seed(2)
+    coords = [torch.from_numpy(g["coords_sigma4"]) + 0.37 * k + 0.1 * torch.randn(1, 2, 16, 18, generator=gen)
+              for k in range(3)]
+    ups = [torch.randn(1, 324, 16, 18, generator=gen) for _ in range(3)]
+    f1r = torch.from_numpy(g["fmap1"]).requires_grad_(True)
+    f2r = torch.from_numpy(g["fmap2"]).requires_grad_(True)
+    rb = tr.TorchCorrBlock(f1r, f2r, 4, 4)
+    sum((rb(c) * u).sum() for c, u in zip(coords, ups)).backward()
+    f1, f2 = _t(g["fmap1"], True), _t(g["fmap2"], True)
+    blk = corr.CorrBlock(f1, f2, precision="fp32")
+    sum((blk(c.cuda()) * u.cuda()).sum() for c, u in zip(coords, ups)).backward()
+    for got, ref in ((f1.grad, f1r.grad), (f2.grad, f2r.grad)):
+        ref = ref.numpy()
+        assert np.allclose(got.cpu().numpy(), ref, rtol=1e-3, atol=1e-4 * np.abs(ref).max())
+
+
+def test_no_grad_builds_no_graph(golden):
+    import corr
+    g = golden("corr_tiny")
+    f1, f2 = _t(g["fmap1"], True), _t(g["fmap2"], True)
+    with torch.no_grad():
+        out = corr.CorrBlock(f1, f2)(_t(g["coords_grid"]))
+    assert not out.requires_grad and out.grad_fn is None
+
+
+@pytest.mark.parametrize("kind", ("grid", "sigma4", "sigma30"))
+def test_alternate_corr_block_matches_corrblock_golden(golden, kind):
+    """AlternateCorrBlock computes the same numbers as CorrBlock (pooling commutes with the dot
+    product); with CorrBlock's coordinate semantics the zero masks agree exactly as well."""
+    import corr
+    g = golden("corr_tiny")
+    with torch.no_grad():
+        blk = corr.AlternateCorrBlock(_t(g["fmap1"]), _t(g["fmap2"]), num_levels=4, radius=4)
+        out = blk(_t(g[f"coords_{kind}"]))
+    assert len(blk.pyramid) == 5 and blk.pyramid[1][1].shape == (1, 8, 8, 9)
+    ref = g[f"out_{kind}"]
+    o = out.cpu().numpy()
+    assert o.shape == ref.shape
+    assert np.array_equal(o == 0, ref == 0)
+    assert rel_max(o, ref) <= 2e-5
+
+
+def test_alt_cuda_corr_module_surface(golden):
+    """alt_cuda_corr.forward/backward: list returns, reference layouts, unscaled, CUDA+contiguous
+    checks raising RuntimeError (correlation.cpp:19-21), floor(coords) semantics."""
+    import alt_cuda_corr
+    g = golden("corr_tiny")
+    f1 = _t(g["fmap1"]).permute(0, 2, 3, 1).contiguous()
+    f2 = _t(g["fmap2"]).permute(0, 2, 3, 1).contiguous()
+    c = _t(g["coords_sigma4"]).permute(0, 2, 3, 1).reshape(1, 1, 16, 18, 2).contiguous()
+    res = alt_cuda_corr.forward(f1, f2, c, 4)
+    assert isinstance(res, list) and len(res) == 1 and res[0].shape == (1, 1, 81, 16, 18)
+    ref = oracle.alt_forward(f1.cpu().numpy(), f2.cpu().numpy(), c.cpu().numpy(), 4, oracle.COORD_DIRECT)
+    assert rel_max(res[0].cpu().numpy(), ref) <= 1e-5
+    assert np.array_equal(res[0].cpu().numpy() == 0, ref == 0)
+    with pytest.raises(RuntimeError, match="contiguous"):
+        alt_cuda_corr.forward(f1.transpose(1, 2), f2, c, 4)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        alt_cuda_corr.forward(f1.cpu(), f2, c, 4)
+    up = torch.randn(res[0].shape, device="cuda")
+    grads = alt_cuda_corr.backward(f1, f2, c, up, 4)
+    assert isinstance(grads, list) and [tuple(t.shape) for t in grads] == [tuple(f1.shape), tuple(f2.shape), tuple(c.shape)]
+
+
+def test_alternate_corr_block_backward():
+    """Gradients of the on-the-fly path vs autograd through its torch restatement (CPU)."""
+    import corr
+    gen = torch.Generator().manual_seed(8)
+    B, D, H, W = 1, 16, 16, 24
+    f1 = torch.randn(B, D, H, W, generator=gen)
+    f2 = torch.randn(B, D, H, W, generator=gen)
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    c = torch.stack([xs, ys]).float()[None] + 3.0 * torch.randn(B, 2, H, W, generator=gen)
+    up = torch.randn(B, 324, H, W, generator=gen)
+    a, b_, cc = f1.clone().requires_grad_(True), f2.clone().requires_grad_(True), c.clone().requires_grad_(True)
+    tr.alt_corr_block_math(a, b_, cc, 4, 4).backward(up)
+    x, y, z = f1.cuda().requires_grad_(True), f2.cuda().requires_grad_(True), c.cuda().requires_grad_(True)
+    out = corr.AlternateCorrBlock(x, y, coord_mode="direct")(z)
+    out.backward(up.cuda())
+    for got, ref in ((x.grad, a.grad), (y.grad, b_.grad), (z.grad, cc.grad)):
+        ref = ref.numpy()
+        assert np.allclose(got.cpu().numpy(), ref, rtol=1e-3, atol=1e-4 * np.abs(ref).max())
