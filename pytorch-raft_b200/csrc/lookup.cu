@@ -11,47 +11,13 @@
 // (c) forms the (2r+1)^2 bilinear samples from shared memory.  Results are transposed through
 // shared memory so the NCHW output (core/corr.py:50) is written as full 128-byte rows.
 #include "common.cuh"
+#include "lookup_common.cuh"
 
 namespace raftcorr {
 
 namespace {
 
-constexpr int kTileQ = 32;   // queries per CTA
-constexpr int kWarps = 8;    // warps per CTA
-constexpr int kFoot = 12;    // staged footprint edge: 2r+1 taps + 1 (bilinear) + 2 (floor flips)
-constexpr int kFootN = kFoot * kFoot;
-constexpr int kFootIters = (kFootN + 31) / 32;
-constexpr int kMaxRd = 9;    // radius <= 4
-constexpr int kOutPitch = kTileQ + 1;
-
-struct LookupParams {
-  LevelDev lv[RAFTCORR_MAX_LEVELS];
-  const float* coords;
-  float* out;
-  int B, H, W, L, r, mode, tiles_x;
-};
-
-struct Tap {
-  int i0;      // floor of the sampling index
-  float frac;  // index - floor
-};
-
-__device__ __forceinline__ Tap make_tap(float centre, int tap_offset, float sm1, float inv,
-                                        float half, int mode) {
-  // core/corr.py:43  coords_lvl = centroid_lvl + delta_lvl  (one fp32 add), then the round trip
-  const float p = __fadd_rn(centre, (float)tap_offset);
-  const float idx = sample_index(p, sm1, inv, half, mode);
-  const float fl = floorf(idx);
-  Tap t;
-  t.i0 = floor_index(fl);
-  t.frac = __fsub_rn(idx, fl);
-  return t;
-}
-
-__device__ __forceinline__ float load_pixel(const float* img, const LevelDev& lv, int gy, int gx) {
-  const bool ok = (gy >= 0) & (gy < lv.H) & (gx >= 0) & (gx < lv.W);
-  return ok ? __ldg(img + (long long)gy * lv.pitch + gx) : 0.0f;
-}
+using namespace lk;
 
 __global__ void __launch_bounds__(kWarps * 32)
 lookup_fwd_kernel(const __grid_constant__ LookupParams p) {
@@ -172,8 +138,15 @@ lookup_fwd_kernel(const __grid_constant__ LookupParams p) {
 
 }  // namespace
 
+int launch_lookup_fwd_tma(const raftcorr_level* levels, int L, const float* coords, float* out, int B,
+                          int H, int W, int r, int mode, cudaStream_t stream);
+
 int launch_lookup_fwd(const raftcorr_level* levels, int L, const float* coords, float* out, int B,
                       int H, int W, int r, int mode, cudaStream_t stream) {
+  // Rows on 16-byte boundaries (raftcorr_pyramid_layout) and r in {3,4}: TMA-gather pipeline.
+  // Any other strides / radii: the generic-stride kernel below (same arithmetic).
+  const int rc = launch_lookup_fwd_tma(levels, L, coords, out, B, H, W, r, mode, stream);
+  if (rc != 1) return rc;
   LookupParams p;
   for (int l = 0; l < L; ++l)
     p.lv[l] = make_level_dev(levels[l].data, levels[l].H, levels[l].W, levels[l].pitch,

@@ -10,7 +10,7 @@ import ctypes
 import os
 
 PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(PKG, "libraftcorr_b200.so")
+LIB_PATH = os.environ.get("RAFTCORR_LIB", os.path.join(PKG, "libraftcorr_b200.so"))
 
 MAX_LEVELS = 4
 COORD_ATEN_CPU, COORD_ATEN_CUDA, COORD_DIRECT = 0, 1, 2

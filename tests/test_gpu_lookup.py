@@ -61,8 +61,11 @@ def test_cfg1_baseline_config(golden):
 @pytest.mark.parametrize("shape", [(8, 55, 128), (2, 47, 156)])
 def test_full_size_against_aten_cuda(shape):
     """BASELINE.json configs[1]/[2] shapes.  Second oracle: the torch restatement of the
-    reference run on the GPU (ATen's CUDA kernels); coord_mode 'aten_cuda' replays its
-    reciprocal-multiply division, so the zero masks must agree exactly."""
+    reference run on the GPU with ATen's native CUDA kernels; coord_mode 'aten_cuda' replays
+    their reciprocal-multiply division, so the zero masks must agree exactly.  (cuDNN is
+    switched off for the reference call: with it on, F.grid_sample dispatches to cuDNN's
+    spatial-transformer sampler, whose undocumented arithmetic differs in the last ulp at
+    integer taps - see DESIGN.md "coordinate semantics".)"""
     B, H, W = shape
     gen = torch.Generator().manual_seed(7)
     pyr = ops.Pyramid(B, H, W, 4, "cuda", zero=True)
@@ -73,7 +76,8 @@ def test_full_size_against_aten_cuda(shape):
     for kind in ("grid", "sigma4", "sigma30"):
         c = coords_for(kind, B, H, W, gen).cuda()
         out = ops.lookup(pyr, c, 4, "aten_cuda")
-        ref = tr.lookup(levels, c, 4)
+        with torch.backends.cudnn.flags(enabled=False):
+            ref = tr.lookup(levels, c, 4)
         assert out.shape == ref.shape == (B, 324, H, W)
         assert out.is_contiguous()
         assert torch.equal(out == 0, ref == 0)

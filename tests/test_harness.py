@@ -1,0 +1,45 @@
+"""Pins the stock-PyTorch RAFT harness to the unmodified reference model (CPU; skipped where
+/root/reference is absent, e.g. on the GPU box), and the oracle's CorrBlock restatement inside
+the full 12-iteration loop."""
+import argparse
+import os
+import sys
+import warnings
+
+import pytest
+import torch
+
+warnings.filterwarnings("ignore")
+REF = "/root/reference/core"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree not present")
+def test_harness_matches_reference_model():
+    from harness.raft_stock import StockRAFT
+    from oracle import torch_restatement as tr
+
+    saved = list(sys.path)
+    saved_mods = {k: sys.modules.pop(k) for k in ("corr", "raft", "utils", "utils.utils", "update", "extractor") if k in sys.modules}
+    sys.path.insert(0, REF)
+    try:
+        from raft import RAFT
+        torch.manual_seed(1234)
+        ref = RAFT(argparse.Namespace(small=False, mixed_precision=False, alternate_corr=False)).eval()
+        mine = StockRAFT().eval()
+        missing = mine.load_state_dict(ref.state_dict(), strict=True)
+        assert not missing.missing_keys and not missing.unexpected_keys
+        gen = torch.Generator().manual_seed(5)
+        im1 = torch.rand(1, 3, 128, 160, generator=gen) * 255
+        im2 = torch.rand(1, 3, 128, 160, generator=gen) * 255
+        with torch.no_grad():
+            lo_ref, up_ref = ref(im1, im2, iters=4, test_mode=True)
+            lo, up = mine(im1, im2, lambda a, b, r: tr.TorchCorrBlock(a, b, 4, r), iters=4)
+        assert up.shape == up_ref.shape == (1, 2, 128, 160)
+        assert (lo - lo_ref).abs().max().item() <= 1e-4
+        epe = (up - up_ref).pow(2).sum(1).sqrt().mean().item()
+        assert epe <= 1e-4, epe
+    finally:
+        sys.path[:] = saved
+        for k in ("corr", "raft", "utils", "utils.utils", "update", "extractor"):
+            sys.modules.pop(k, None)
+        sys.modules.update(saved_mods)
