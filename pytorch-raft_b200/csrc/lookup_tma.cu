@@ -14,6 +14,11 @@
 //   CTA = 1 SM, persistent over tiles of 32 consecutive-x queries
 //   warp 16        producer: coords -> box origins -> 128 TMA loads per tile
 //   warps 0..15    consumers: tap tables, bilinear samples, transposed store
+#include <string.h>
+
+#include <atomic>
+#include <mutex>
+
 #include "lookup_common.cuh"
 #include "tma_util.cuh"
 
@@ -23,250 +28,316 @@ namespace {
 
 using namespace lk;
 
-constexpr int kConsumers = 16;                        // consumer warps = queries per stage
-constexpr int kThreadsTma = (kConsumers + 1) * 32;
-constexpr int kStageQ = 16;                           // queries per pipeline stage (half a tile)
-constexpr int kStagesTma = 3;
-constexpr int kSlotBytes = 768;                       // 16 x 12 fp32 box
-constexpr int kStageBytes = kStageQ * RAFTCORR_MAX_LEVELS * kSlotBytes;  // 48 KB
+constexpr int kWarpsTma = 16;                         // one query per warp per pipeline unit
+constexpr int kThreadsTma = kWarpsTma * 32;
+constexpr int kUnitQ = 16;                            // queries per unit (half an output tile)
+constexpr int kDepth = 3;                             // window buffers per warp (2 units in flight)
+constexpr int kAuxOff = 160;                          // floats; aux box (4 x 12) starts 640 B in
+constexpr int kSlotBytes = 896;                       // per (warp, level): main 576 B | aux 192 B
+constexpr int kWarpBufBytes = RAFTCORR_MAX_LEVELS * kSlotBytes;
 constexpr int kBoxHeights = 3;                        // 10, 11, 12 rows
-constexpr int kBoxWidths = 2;                         // 12 or 16 columns
 
 // TMA tile loads need the innermost start coordinate on a 16-byte boundary (x % 4 == 0 for
-// fp32), so a window whose first column is x_lo is fetched from x_lo & ~3: 12 columns suffice
-// when (x_lo & 3) + width <= 12, else 16.  Heights 10..12 cover the floor flips of the
-// coordinate round trip.  One tensor map per (level, width, height).
+// fp32).  A window whose first column is x_lo is therefore fetched from bx = x_lo & ~3 as a
+// 12-column box, plus a 4-column box at bx + 12 when (x_lo & 3) + width > 12.  Heights 10..12
+// cover the floor flips of the coordinate round trip.  Row pitch 12 keeps the 27 active lanes
+// of the sampling phase on distinct banks.
 struct alignas(64) LookupTmaMaps {
-  CUtensorMap m[RAFTCORR_MAX_LEVELS][kBoxWidths][kBoxHeights];
+  CUtensorMap main[RAFTCORR_MAX_LEVELS][kBoxHeights];
+  CUtensorMap aux[RAFTCORR_MAX_LEVELS][kBoxHeights];
 };
 
 struct LookupTmaParams {
   LevelDev lv[RAFTCORR_MAX_LEVELS];
   const float* coords;
   float* out;
-  int B, H, W, L, mode, tiles_x;
+  int B, H, W, mode, tiles_x;
   long long tiles;
 };
 
-template <int R>
+template <int R, int L>
 struct Cfg {
   static constexpr int kRd = 2 * R + 1;
   static constexpr int kRd2 = kRd * kRd;
-  static constexpr int kJGroup = 3;                               // outputs per lane along y
-  static constexpr int kJBlocks = (kRd + kJGroup - 1) / kJGroup;  // 3
-  static constexpr int kActive = kRd * kJBlocks;                  // lanes with work (27 or 21)
-  static constexpr int kOutBytes = ((RAFTCORR_MAX_LEVELS * kRd2 * kOutPitch * 4 + 127) / 128) * 128;
-  static constexpr int kTabBytes = kConsumers * RAFTCORR_MAX_LEVELS * 2 * kMaxRd * 8;
-  static constexpr int kOffOut = kStagesTma * kStageBytes;
+  static constexpr int kChannels = L * kRd2;
+  static constexpr int kTaps = L * 2 * kRd;                      // tap coordinates per query
+  static constexpr int kTapRounds = (kTaps + 31) / 32;
+  static constexpr int kIGroups = 3;                             // x taps per lane: i = ib + 3*ii
+  static constexpr int kIPer = (kRd + kIGroups - 1) / kIGroups;
+  static constexpr int kActive = kRd * kIGroups;                 // lanes with work (27 or 21)
+  static constexpr int kOffOut = kDepth * kWarpsTma * kWarpBufBytes;
+  static constexpr int kOutBytes = ((kChannels * kOutPitch * 4 + 127) / 128) * 128;
   static constexpr int kOffTab = kOffOut + kOutBytes;
-  static constexpr int kOffCoords = kOffTab + kTabBytes;
-  static constexpr int kOffBars = kOffCoords + kStagesTma * kStageQ * 8;
-  static constexpr int kSmem = kOffBars + 64;
+  static constexpr int kTabBytes = kWarpsTma * RAFTCORR_MAX_LEVELS * 2 * kMaxRd * 8;
+  static constexpr int kOffCoords = kOffTab + kTabBytes;         // [warp][depth] float2
+  static constexpr int kOffBars = kOffCoords + kWarpsTma * kDepth * 8;
+  static constexpr int kSmem = kOffBars + kWarpsTma * kDepth * 8;
 };
 
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
-// Window geometry of one (query, level): derived from the first and last tap of each axis with
-// the same arithmetic on the producer and the consumer side, so both agree on the box.
+// Window geometry of one (query, level), derived from the first and last tap of each axis.
 struct Window {
-  int x_lo, y_lo;   // floor index of tap -R
-  int wdt, hgt;     // columns / rows the 2R+1 taps (+1 for bilinear) span
+  int x_lo, y_lo;   // floor index of tap -R per axis
   int ox;           // x_lo - box start (0..3)
-  int wsel, hsel;   // which tensor map
-  int pitch;        // staged row pitch in floats (12 or 16)
-  bool fast;        // window fits the staged box
+  int hsel;         // box height - 10
+  bool need_aux;    // columns 12..15 of the box are touched
+  bool fast;        // window fits the staged boxes
 };
 
 __device__ __forceinline__ Window make_window(int x_lo, int x_last, int y_lo, int y_last) {
   Window w;
+  const int wdt = x_last + 2 - x_lo, hgt = y_last + 2 - y_lo;
   w.x_lo = x_lo;
   w.y_lo = y_lo;
-  w.wdt = x_last + 2 - x_lo;
-  w.hgt = y_last + 2 - y_lo;
-  w.fast = (w.wdt >= 1) & (w.wdt <= kFoot) & (w.hgt >= 1) & (w.hgt <= kFoot);
+  w.fast = (wdt >= 1) & (wdt <= kFoot) & (hgt >= 1) & (hgt <= kFoot);
   w.ox = x_lo & 3;  // two's complement: also right for negative x_lo
-  w.wsel = (w.ox + w.wdt > 12) ? 1 : 0;
-  w.pitch = w.wsel ? 16 : 12;
-  const int h = w.hgt < 10 ? 10 : (w.hgt > 12 ? 12 : w.hgt);
+  w.need_aux = w.ox + wdt > kFoot;
+  const int h = hgt < 10 ? 10 : (hgt > 12 ? 12 : hgt);
   w.hsel = h - 10;
   return w;
 }
 
-template <int R>
+// rare path: |coords| so large that fp32 spacing breaks the window; sample straight from global
+__device__ __noinline__ float sample_direct(const LevelDev& lv, long long q, Tap a, Tap c) {
+  const float* img = lv.data + q * lv.istride;
+  return bilinear_combine(load_pixel(img, lv, c.i0, a.i0), load_pixel(img, lv, c.i0, a.i0 + 1),
+                          load_pixel(img, lv, c.i0 + 1, a.i0), load_pixel(img, lv, c.i0 + 1, a.i0 + 1),
+                          a.frac, c.frac);
+}
+
+template <int R, int L>
 __global__ void __launch_bounds__(kThreadsTma, 1)
 lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_constant__ LookupTmaMaps maps) {
-  using C = Cfg<R>;
+  using C = Cfg<R, L>;
   constexpr int rd = C::kRd, rd2 = C::kRd2;
   extern __shared__ __align__(1024) unsigned char smem[];
   const uint32_t smem_base = smem_u32(smem);
-  float* out_s = reinterpret_cast<float*>(smem + C::kOffOut);
-  float2* coords_s = reinterpret_cast<float2*>(smem + C::kOffCoords);  // [stages][16]
-  const uint32_t bars = smem_base + C::kOffBars;
-  auto full_bar = [&](int s) { return bars + 8 * s; };
-  auto empty_bar = [&](int s) { return bars + 8 * (kStagesTma + s); };
-
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < kStagesTma; ++s) {
-      mbar_init(full_bar(s), 32);             // one arrive (+ its bytes) per producer lane
-      mbar_init(empty_bar(s), kConsumers);    // one arrive per consumer warp
-    }
+  float* out_s = reinterpret_cast<float*>(smem + C::kOffOut);
+  Tap* tab = reinterpret_cast<Tap*>(smem + C::kOffTab) + warp * (RAFTCORR_MAX_LEVELS * 2 * kMaxRd);
+  float2* coords_w = reinterpret_cast<float2*>(smem + C::kOffCoords) + warp * kDepth;
+  const uint32_t bar0 = smem_base + C::kOffBars + warp * kDepth * 8;   // this warp's mbarriers
+
+  if (lane == 0) {
+    for (int s = 0; s < kDepth; ++s) mbar_init(bar0 + 8 * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
 
   const long long N = (long long)p.H * p.W;
-  const int nC = p.L * rd2;
+  const long long n_tiles = (p.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;  // tiles of this CTA
+  const long long n_units = 2 * n_tiles;
 
-  if (warp == kConsumers) {
-    // ------------------------------ producer ------------------------------
-    // lane = (level pair, query): lanes 0-15 fetch levels 0,1 and lanes 16-31 levels 2,3
-    const int pq = lane & 15, l0 = (lane >> 4) * 2;
-    uint32_t u = 0;
-    for (long long tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-      const int xt = (int)(tile % p.tiles_x);
-      const int y = (int)((tile / p.tiles_x) % p.H);
-      const int b = (int)(tile / ((long long)p.tiles_x * p.H));
-      for (int half = 0; half < 2; ++half, ++u) {
-        const int stage = u % kStagesTma;
-        const uint32_t ph = (u / kStagesTma) & 1;
-        const int x = xt * kTileQ + half * kStageQ + pq;
-        const bool valid = x < p.W;
-        const long long pix = (long long)y * p.W + (valid ? x : 0);
-        const float cx = __ldg(p.coords + ((long long)b * 2 + 0) * N + pix);
-        const float cy = __ldg(p.coords + ((long long)b * 2 + 1) * N + pix);
-        mbar_wait(empty_bar(stage), ph ^ 1, 1);
-        if (lane < kStageQ) coords_s[stage * kStageQ + pq] = make_float2(cx, cy);
-        int bx[2], by[2], ws[2], hs[2];
-        uint32_t bytes = 0;
+  // unit -> (b, y, x) of this warp's query
+  auto locate = [&](long long u, int& b, int& y, int& x) {
+    const long long tile = blockIdx.x + (u >> 1) * gridDim.x;
+    const int xt = (int)(tile % p.tiles_x);
+    y = (int)((tile / p.tiles_x) % p.H);
+    b = (int)(tile / ((long long)p.tiles_x * p.H));
+    x = xt * kTileQ + (int)(u & 1) * kUnitQ + warp;
+  };
+  auto load_coords = [&](long long u, float& cx, float& cy) {
+    int b, y, x;
+    cx = cy = 0.0f;
+    if (u < n_units) {
+      locate(u, b, y, x);
+      if (x < p.W) {
+        const long long pix = (long long)y * p.W + x;
+        cx = __ldg(p.coords + ((long long)b * 2 + 0) * N + pix);
+        cy = __ldg(p.coords + ((long long)b * 2 + 1) * N + pix);
+      }
+    }
+  };
+  // issue the window loads of unit u into buffer u % kDepth
+  auto issue = [&](long long u, float cx, float cy) {
+    int b, y, x;
+    locate(u, b, y, x);
+    if (x >= p.W) return;
+    const int s = (int)(u % kDepth);
+    if (lane == 0) coords_w[s] = make_float2(cx, cy);
+    // lanes 0..4L-1: (level, {x first, x last, y first, y last}) tap floors
+    int fl = 0;
+    {
+      const int l = (lane >> 2) < L ? (lane >> 2) : 0;
+      const LevelDev& lv = p.lv[l];
+      const bool is_y = lane & 2;
+      const float c = __fmul_rn(is_y ? cy : cx, lv.inv_pow2);
+      fl = make_tap(c, (lane & 1) ? R : -R, is_y ? lv.sm1y : lv.sm1x, is_y ? lv.invy : lv.invx,
+                    is_y ? lv.halfy : lv.halfx, p.mode).i0;
+    }
+    const int l = lane < L ? lane : 0;
+    const Window w = make_window(__shfl_sync(0xffffffffu, fl, 4 * l), __shfl_sync(0xffffffffu, fl, 4 * l + 1),
+                                 __shfl_sync(0xffffffffu, fl, 4 * l + 2), __shfl_sync(0xffffffffu, fl, 4 * l + 3));
+    uint32_t bytes = lane < L ? (uint32_t)((10 + w.hsel) * (48 + (w.need_aux ? 16 : 0))) : 0u;
+    bytes += __shfl_xor_sync(0xffffffffu, bytes, 1);
+    bytes += __shfl_xor_sync(0xffffffffu, bytes, 2);
+    const uint32_t bar = bar0 + 8 * s;
+    if (lane == 0) mbar_expect_tx(bar, bytes);
+    __syncwarp();
+    if (lane < L) {
+      const LevelDev& lv = p.lv[lane];
+      // windows entirely outside the image are all zeros wherever the box sits
+      const int bx = max(-64, min(w.x_lo - w.ox, (lv.W + 64) & ~3));
+      const int by = max(-64, min(w.y_lo, lv.H + 64));
+      const int q = (int)((long long)b * N + (long long)y * p.W + x);
+      const uint32_t dst = smem_base + (s * kWarpsTma + warp) * kWarpBufBytes + lane * kSlotBytes;
+      tma_load_3d(dst, &maps.main[lane][w.hsel], bar, bx, by, q);
+      if (w.need_aux) tma_load_3d(dst + kAuxOff * 4, &maps.aux[lane][w.hsel], bar, bx + kFoot, by, q);
+    }
+  };
+
+  // per-lane description of the tap this lane evaluates in each round of the tap-table phase
+  float t_sm1[C::kTapRounds], t_inv[C::kTapRounds], t_half[C::kTapRounds], t_pow[C::kTapRounds];
+  int t_off[C::kTapRounds], t_slot[C::kTapRounds];
+  bool t_isy[C::kTapRounds];
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
-          const int l = l0 + k;
-          bx[k] = by[k] = ws[k] = hs[k] = 0;
-          if (valid && l < p.L) {
-            const LevelDev& lv = p.lv[l];
-            const float lx = __fmul_rn(cx, lv.inv_pow2), ly = __fmul_rn(cy, lv.inv_pow2);
-            const Window w = make_window(make_tap(lx, -R, lv.sm1x, lv.invx, lv.halfx, p.mode).i0,
-                                         make_tap(lx, R, lv.sm1x, lv.invx, lv.halfx, p.mode).i0,
-                                         make_tap(ly, -R, lv.sm1y, lv.invy, lv.halfy, p.mode).i0,
-                                         make_tap(ly, R, lv.sm1y, lv.invy, lv.halfy, p.mode).i0);
-            // windows entirely outside the image are all zeros wherever the box sits
-            bx[k] = max(-64, min(w.x_lo - w.ox, (lv.W + 64) & ~3));
-            by[k] = max(-64, min(w.y_lo, lv.H + 64));
-            ws[k] = w.wsel;
-            hs[k] = w.hsel;
-            bytes += (uint32_t)(w.pitch * 4 * (10 + w.hsel));
-          }
+  for (int r = 0; r < C::kTapRounds; ++r) {
+    const int t = r * 32 + lane;
+    const int tt = t < C::kTaps ? t : 0;
+    const int l = tt / (2 * rd);
+    const int rem = tt - l * 2 * rd;
+    const int axis = rem >= rd;
+    const int tap = rem - axis * rd;
+    const LevelDev& lv = p.lv[l];
+    t_sm1[r] = axis ? lv.sm1y : lv.sm1x;
+    t_inv[r] = axis ? lv.invy : lv.invx;
+    t_half[r] = axis ? lv.halfy : lv.halfx;
+    t_pow[r] = lv.inv_pow2;
+    t_off[r] = tap - R;
+    t_isy[r] = axis;
+    t_slot[r] = t < C::kTaps ? (l * 2 + axis) * kMaxRd + tap : -1;
+  }
+  // sampling phase: lane = j * 3 + ib handles y tap j and x taps i = ib + 3 * ii
+  const int tj = lane / C::kIGroups;
+  const int tib = lane - tj * C::kIGroups;
+
+  {  // prologue: two units in flight
+    float cx, cy;
+    for (int u = 0; u < 2; ++u)
+      if (u < n_units) {
+        load_coords(u, cx, cy);
+        issue(u, cx, cy);
+      }
+  }
+  float ncx, ncy;
+  load_coords(2, ncx, ncy);
+  uint32_t phases = 0;  // bit s = parity of the next completion of this warp's buffer s
+
+  for (long long u = 0; u < n_units; ++u) {
+    if (u + 2 < n_units) issue(u + 2, ncx, ncy);
+    load_coords(u + 3, ncx, ncy);
+
+    int b, y, x;
+    locate(u, b, y, x);
+    const int s = (int)(u % kDepth);
+    const int qi = (int)(u & 1) * kUnitQ + warp;
+    if (x < p.W) {
+      mbar_wait(bar0 + 8 * s, (phases >> s) & 1u, 2);
+      phases ^= 1u << s;
+      const float2 cxy = coords_w[s];
+#pragma unroll
+      for (int r = 0; r < C::kTapRounds; ++r) {
+        if (t_slot[r] >= 0) {
+          const float c = __fmul_rn(t_isy[r] ? cxy.y : cxy.x, t_pow[r]);
+          tab[t_slot[r]] = make_tap(c, t_off[r], t_sm1[r], t_inv[r], t_half[r], p.mode);
         }
-        if (bytes) mbar_expect_tx(full_bar(stage), bytes); else mbar_arrive(full_bar(stage));
-        if (valid) {
-          const int q = (int)((long long)b * N + pix);
-          const uint32_t dst0 = smem_base + stage * kStageBytes + pq * (RAFTCORR_MAX_LEVELS * kSlotBytes);
+      }
+      __syncwarp();
+      const float* buf = reinterpret_cast<const float*>(smem + (s * kWarpsTma + warp) * kWarpBufBytes);
 #pragma unroll
-          for (int k = 0; k < 2; ++k)
-            if (l0 + k < p.L)
-              tma_load_3d(dst0 + (l0 + k) * kSlotBytes, &maps.m[l0 + k][ws[k]][hs[k]], full_bar(stage),
-                          bx[k], by[k], q);
+      for (int l = 0; l < L; ++l) {
+        const Tap* tx = tab + (l * 2 + 0) * kMaxRd;
+        const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
+        const Window w = make_window(tx[0].i0, tx[rd - 1].i0, ty[0].i0, ty[rd - 1].i0);
+        if (lane < C::kActive) {
+          const Tap c = ty[tj];
+          const float* f = buf + l * (kSlotBytes / 4);
+          const int r0 = (c.i0 - w.y_lo) * kFoot;        // main row offset; aux rows have pitch 4
+          float* o = out_s + (l * rd2 + tj) * kOutPitch + qi;
+#pragma unroll
+          for (int ii = 0; ii < C::kIPer; ++ii) {
+            const int i = tib + C::kIGroups * ii;
+            if (i < rd) {
+              const Tap a = tx[i];
+              float v;
+              if (w.fast) {
+                const int c0 = w.ox + (a.i0 - w.x_lo), c1 = c0 + 1;   // box columns of the two corners
+                const int o0 = c0 < kFoot ? r0 + c0 : kAuxOff + (r0 / 3) + (c0 - kFoot);
+                const int o1 = c1 < kFoot ? r0 + c1 : kAuxOff + (r0 / 3) + (c1 - kFoot);
+                const int d0 = c0 < kFoot ? kFoot : 4, d1 = c1 < kFoot ? kFoot : 4;
+                v = bilinear_combine(f[o0], f[o1], f[o0 + d0], f[o1 + d1], a.frac, c.frac);
+              } else {
+                v = sample_direct(p.lv[l], (long long)b * N + (long long)y * p.W + x, a, c);
+              }
+              o[i * rd * kOutPitch] = v;
+            }
+          }
         }
       }
     }
-  } else {
-    // ------------------------------ consumers ------------------------------
-    Tap* tab = reinterpret_cast<Tap*>(smem + C::kOffTab) + warp * (RAFTCORR_MAX_LEVELS * 2 * kMaxRd);
-    const int ti = lane / C::kJBlocks;            // x tap of this lane
-    const int tj0 = (lane - ti * C::kJBlocks) * C::kJGroup;  // first y tap of this lane
-    uint32_t u = 0;
-    for (long long tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
-      const int xt = (int)(tile % p.tiles_x);
-      const int y = (int)((tile / p.tiles_x) % p.H);
-      const int b = (int)(tile / ((long long)p.tiles_x * p.H));
-      const int x0 = xt * kTileQ;
-      for (int half = 0; half < 2; ++half, ++u) {
-        const int stage = u % kStagesTma;
-        const uint32_t ph = (u / kStagesTma) & 1;
-        const int qi = half * kStageQ + warp;     // this warp's query within the tile
-        mbar_wait(full_bar(stage), ph, 2);
-        if (x0 + qi < p.W) {
-          const float2 cxy = coords_s[stage * kStageQ + warp];
-          // tap tables: L * 2 * rd coordinates, one per lane per round
-#pragma unroll
-          for (int t0 = 0; t0 < RAFTCORR_MAX_LEVELS * 2 * rd; t0 += 32) {
-            const int t = t0 + lane;
-            if (t < p.L * 2 * rd) {
-              const int l = t / (2 * rd);
-              const int rem = t - l * 2 * rd;
-              const int axis = rem >= rd;
-              const int tap = rem - axis * rd;
-              const LevelDev& lv = p.lv[l];
-              const float c = __fmul_rn(axis ? cxy.y : cxy.x, lv.inv_pow2);
-              tab[(l * 2 + axis) * kMaxRd + tap] =
-                  axis ? make_tap(c, tap - R, lv.sm1y, lv.invy, lv.halfy, p.mode)
-                       : make_tap(c, tap - R, lv.sm1x, lv.invx, lv.halfx, p.mode);
-            }
-          }
-          __syncwarp();
-          const float* slot0 = reinterpret_cast<const float*>(smem + stage * kStageBytes +
-                                                              warp * (RAFTCORR_MAX_LEVELS * kSlotBytes));
-#pragma unroll
-          for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
-            if (l < p.L) {
-              const Tap* tx = tab + (l * 2 + 0) * kMaxRd;
-              const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
-              const Window w = make_window(tx[0].i0, tx[rd - 1].i0, ty[0].i0, ty[rd - 1].i0);
-              if (lane < C::kActive) {
-                const Tap a = tx[ti];
-                const float* f = slot0 + l * (kSlotBytes / 4) + w.ox;
-#pragma unroll
-                for (int jj = 0; jj < C::kJGroup; ++jj) {
-                  const int j = tj0 + jj;
-                  if (j < rd) {
-                    const Tap c = ty[j];
-                    float vnw, vne, vsw, vse;
-                    if (w.fast) {
-                      const float* g = f + (c.i0 - w.y_lo) * w.pitch + (a.i0 - w.x_lo);
-                      vnw = g[0];
-                      vne = g[1];
-                      vsw = g[w.pitch];
-                      vse = g[w.pitch + 1];
-                    } else {  // |coords| so large that fp32 spacing breaks the window
-                      const LevelDev& lv = p.lv[l];
-                      const long long q = (long long)b * N + (long long)y * p.W + x0 + qi;
-                      const float* img = lv.data + q * lv.istride;
-                      vnw = load_pixel(img, lv, c.i0, a.i0);
-                      vne = load_pixel(img, lv, c.i0, a.i0 + 1);
-                      vsw = load_pixel(img, lv, c.i0 + 1, a.i0);
-                      vse = load_pixel(img, lv, c.i0 + 1, a.i0 + 1);
-                    }
-                    out_s[(l * rd2 + ti * rd + j) * kOutPitch + qi] =
-                        bilinear_combine(vnw, vne, vsw, vse, a.frac, c.frac);
-                  }
-                }
-              }
-            }
-          }
-        }
-        // this warp is done with the stage's windows: hand the buffers back to the producer
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty_bar(stage));
+    if (u & 1) {  // both halves of the output tile are in shared memory: write it out
+      __syncwarp();
+      named_bar_sync(1, kThreadsTma);
+      const long long tile = blockIdx.x + (u >> 1) * gridDim.x;
+      const int x0 = (int)(tile % p.tiles_x) * kTileQ;
+      const int xx = x0 + lane;
+      if (xx < p.W) {
+        float* dst = p.out + (long long)b * C::kChannels * N + (long long)y * p.W + xx;
+#pragma unroll 4
+        for (int c = warp; c < C::kChannels; c += kWarpsTma)
+          __stcs(dst + (long long)c * N, out_s[c * kOutPitch + lane]);
       }
-      named_bar_sync(1, kConsumers * 32);
-      {
-        const int x = x0 + lane;
-        if (x < p.W) {
-          float* dst = p.out + (long long)b * nC * N + (long long)y * p.W + x;
-          for (int c = warp; c < nC; c += kConsumers)
-            __stcs(dst + (long long)c * N, out_s[c * kOutPitch + lane]);
-        }
-      }
-      named_bar_sync(1, kConsumers * 32);
+      named_bar_sync(1, kThreadsTma);
+    } else {
+      __syncwarp();
     }
   }
 }
 
+struct MapKey {
+  const void* data[RAFTCORR_MAX_LEVELS];
+  long long pitch[RAFTCORR_MAX_LEVELS], istride[RAFTCORR_MAX_LEVELS], bn;
+  int h[RAFTCORR_MAX_LEVELS], w[RAFTCORR_MAX_LEVELS];
+};
+constexpr int kMapCacheSize = 8;
+struct MapCache {
+  std::mutex mu;
+  MapKey keys[kMapCacheSize];
+  LookupTmaMaps maps[kMapCacheSize];
+  unsigned long long stamp[kMapCacheSize] = {};
+  unsigned long long clock = 0;
+};
+MapCache& map_cache() {
+  static MapCache c;
+  return c;
+}
+bool map_cache_get(const MapKey& k, LookupTmaMaps* out) {
+  MapCache& c = map_cache();
+  std::lock_guard<std::mutex> g(c.mu);
+  for (int i = 0; i < kMapCacheSize; ++i)
+    if (c.stamp[i] && memcmp(&c.keys[i], &k, sizeof(MapKey)) == 0) {
+      c.stamp[i] = ++c.clock;
+      *out = c.maps[i];
+      return true;
+    }
+  return false;
+}
+void map_cache_put(const MapKey& k, const LookupTmaMaps& m) {
+  MapCache& c = map_cache();
+  std::lock_guard<std::mutex> g(c.mu);
+  int victim = 0;
+  for (int i = 1; i < kMapCacheSize; ++i)
+    if (c.stamp[i] < c.stamp[victim]) victim = i;
+  c.keys[victim] = k;
+  c.maps[victim] = m;
+  c.stamp[victim] = ++c.clock;
+}
+
 bool tma_eligible(const raftcorr_level* levels, int L, int r) {
-  if (r != 3 && r != 4) return false;
+  if (L != RAFTCORR_MAX_LEVELS || (r != 3 && r != 4)) return false;
   for (int l = 0; l < L; ++l) {
     if ((levels[l].pitch & 3) || (levels[l].image_stride & 3)) return false;
     if (reinterpret_cast<uintptr_t>(levels[l].data) & 15) return false;
@@ -274,15 +345,20 @@ bool tma_eligible(const raftcorr_level* levels, int L, int r) {
   return get_encode() != nullptr;
 }
 
-template <int R>
+template <int R, int L>
 int launch_tma(const LookupTmaParams& p, const LookupTmaMaps& maps, cudaStream_t stream) {
-  using C = Cfg<R>;
-  RC_CHECK_CUDA(cudaFuncSetAttribute(lookup_fwd_tma_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
-  int dev = 0, sms = 0;
+  using C = Cfg<R, L>;
+  int dev = 0;
   RC_CHECK_CUDA(cudaGetDevice(&dev));
-  RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  static std::atomic<int> sm_count[64];  // per device: 0 = kernel attribute not set yet
+  int sms = (dev >= 0 && dev < 64) ? sm_count[dev].load(std::memory_order_acquire) : 0;
+  if (sms == 0) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(lookup_fwd_tma_kernel<R, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
+    RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (dev >= 0 && dev < 64) sm_count[dev].store(sms, std::memory_order_release);
+  }
   const int grid = (int)(p.tiles < sms ? p.tiles : sms);
-  lookup_fwd_tma_kernel<R><<<grid, kThreadsTma, C::kSmem, stream>>>(p, maps);
+  lookup_fwd_tma_kernel<R, L><<<grid, kThreadsTma, C::kSmem, stream>>>(p, maps);
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -300,33 +376,53 @@ int launch_lookup_fwd_tma(const raftcorr_level* levels, int L, const float* coor
                           int H, int W, int r, int mode, cudaStream_t stream) {
   if (!tma_eligible(levels, L, r)) return 1;
   LookupTmaParams p;
-  LookupTmaMaps maps;
   const long long BN = (long long)B * H * W;
+  if (BN >= (1LL << 31)) return 1;
+  for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l)
+    p.lv[l] = make_level_dev(levels[l].data, levels[l].H, levels[l].W, levels[l].pitch,
+                             levels[l].image_stride, l);
+  // Tensor maps depend only on (pointers, sizes, strides); encoding 24 of them costs tens of
+  // microseconds of host time, more than the kernel itself, and RAFT calls the lookup once per
+  // refinement iteration on the same pyramid: keep the last few sets (mutex-protected, so the
+  // library stays re-entrant under nn.DataParallel's one-thread-per-GPU calls).
+  MapKey key;
+  memset(&key, 0, sizeof(key));
+  key.bn = BN;
   for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
-    const int s = l < L ? l : 0;
-    p.lv[l] = make_level_dev(levels[s].data, levels[s].H, levels[s].W, levels[s].pitch,
-                             levels[s].image_stride, s);
-    cuuint64_t dims[3] = {(cuuint64_t)levels[s].W, (cuuint64_t)levels[s].H, (cuuint64_t)BN};
-    cuuint64_t strides[2] = {(cuuint64_t)levels[s].pitch * 4, (cuuint64_t)levels[s].image_stride * 4};
-    for (int wi = 0; wi < kBoxWidths; ++wi)
+    key.data[l] = levels[l].data;
+    key.h[l] = levels[l].H;
+    key.w[l] = levels[l].W;
+    key.pitch[l] = levels[l].pitch;
+    key.istride[l] = levels[l].image_stride;
+  }
+  LookupTmaMaps maps;
+  if (!map_cache_get(key, &maps)) {
+    for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
+      cuuint64_t dims[3] = {(cuuint64_t)levels[l].W, (cuuint64_t)levels[l].H, (cuuint64_t)BN};
+      cuuint64_t strides[2] = {(cuuint64_t)levels[l].pitch * 4, (cuuint64_t)levels[l].image_stride * 4};
       for (int h = 0; h < kBoxHeights; ++h) {
-        cuuint32_t box[3] = {(cuuint32_t)(wi ? 16 : 12), (cuuint32_t)(10 + h), 1};
-        if (int rc = encode(&maps.m[l][wi][h], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, levels[s].data, dims,
-                            strides, box, CU_TENSOR_MAP_SWIZZLE_NONE, "lookup level"))
+        cuuint32_t box[3] = {(cuuint32_t)kFoot, (cuuint32_t)(10 + h), 1};
+        if (int rc = encode(&maps.main[l][h], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, levels[l].data, dims, strides,
+                            box, CU_TENSOR_MAP_SWIZZLE_NONE, "lookup window", CU_TENSOR_MAP_L2_PROMOTION_NONE))
+          return rc;
+        box[0] = 4;
+        if (int rc = encode(&maps.aux[l][h], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, levels[l].data, dims, strides,
+                            box, CU_TENSOR_MAP_SWIZZLE_NONE, "lookup window tail", CU_TENSOR_MAP_L2_PROMOTION_NONE))
           return rc;
       }
+    }
+    map_cache_put(key, maps);
   }
   p.coords = coords;
   p.out = out;
   p.B = B;
   p.H = H;
   p.W = W;
-  p.L = L;
   p.mode = mode;
   p.tiles_x = (W + kTileQ - 1) / kTileQ;
   p.tiles = (long long)B * H * p.tiles_x;
   if (p.tiles == 0) return 0;
-  return r == 4 ? launch_tma<4>(p, maps, stream) : launch_tma<3>(p, maps, stream);
+  return r == 4 ? launch_tma<4, 4>(p, maps, stream) : launch_tma<3, 4>(p, maps, stream);
 }
 
 }  // namespace raftcorr

@@ -122,12 +122,13 @@ inline EncodeTiledFn get_encode() {
 }
 
 inline int encode(CUtensorMap* m, CUtensorMapDataType dt, int rank, void* base, const cuuint64_t* dims,
-           const cuuint64_t* strides, const cuuint32_t* box, CUtensorMapSwizzle sw, const char* what) {
+           const cuuint64_t* strides, const cuuint32_t* box, CUtensorMapSwizzle sw, const char* what,
+                  CUtensorMapL2promotion l2 = CU_TENSOR_MAP_L2_PROMOTION_L2_128B) {
   EncodeTiledFn fn = get_encode();
   if (!fn) return fail(RAFTCORR_E_DRIVER, "cuTensorMapEncodeTiled is not available from this driver");
   cuuint32_t ones[5] = {1, 1, 1, 1, 1};
   const CUresult r = fn(m, dt, (cuuint32_t)rank, base, dims, strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        sw, l2, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(RAFTCORR_E_INVALID, "cuTensorMapEncodeTiled(%s) failed: CUresult %d", what, (int)r);
   return 0;
 }

@@ -45,6 +45,22 @@ def _stream(t: torch.Tensor) -> ctypes.c_void_p:
     return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
 
 
+class _on_device:
+    """`with torch.cuda.device(d)` only when d is not already current (the context manager
+    costs more host time than a lookup kernel runs)."""
+
+    def __init__(self, device):
+        self.ctx = None if device.index == torch.cuda.current_device() else torch.cuda.device(device)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+
+
 def _require_cuda_f32(t: torch.Tensor, name: str) -> None:
     if not t.is_cuda:
         raise RuntimeError(f"{name} must be a CUDA tensor")
@@ -106,7 +122,7 @@ def lookup(pyr: Pyramid, coords: torch.Tensor, radius: int, coord_mode=None) -> 
     coords = coords.contiguous()
     rd = 2 * radius + 1
     out = torch.empty((B, pyr.num_levels * rd * rd, H, W), dtype=torch.float32, device=coords.device)
-    with torch.cuda.device(coords.device):
+    with _on_device(coords.device):
         _capi.check(_capi.lib().raftcorr_lookup_fwd(pyr.desc, pyr.num_levels, coords.data_ptr(), out.data_ptr(),
                                                     B, H, W, radius, resolve_coord_mode(coord_mode),
                                                     _stream(coords)), "raftcorr_lookup_fwd")
