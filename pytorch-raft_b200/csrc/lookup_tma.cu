@@ -31,27 +31,26 @@ using namespace lk;
 constexpr int kWarpsTma = 16;                         // one query per warp per pipeline unit
 constexpr int kThreadsTma = kWarpsTma * 32;
 constexpr int kUnitQ = 16;                            // queries per unit (half an output tile)
-constexpr int kDepth = 3;                             // window buffers per warp (2 units in flight)
-constexpr int kAuxOff = 160;                          // floats; aux box (4 x 12) starts 640 B in
-constexpr int kSlotBytes = 896;                       // per (warp, level): main 576 B | aux 192 B
+constexpr int kDepth = 3;                             // units buffered per warp (2 in flight)
+constexpr int kBoxW = 16;                             // staged window: 16 columns ...
+constexpr int kSlotBytes = kBoxW * kFoot * 4;         // ... x up to 12 rows of fp32 = 768 B
 constexpr int kWarpBufBytes = RAFTCORR_MAX_LEVELS * kSlotBytes;
 constexpr int kBoxHeights = 3;                        // 10, 11, 12 rows
+constexpr int kTabEntries = RAFTCORR_MAX_LEVELS * 2 * kMaxRd;
 
 // TMA tile loads need the innermost start coordinate on a 16-byte boundary (x % 4 == 0 for
-// fp32).  A window whose first column is x_lo is therefore fetched from bx = x_lo & ~3 as a
-// 12-column box, plus a 4-column box at bx + 12 when (x_lo & 3) + width > 12.  Heights 10..12
-// cover the floor flips of the coordinate round trip.  Row pitch 12 keeps the 27 active lanes
-// of the sampling phase on distinct banks.
+// fp32): a window whose first column is x_lo is fetched from bx = x_lo & ~3 as a 16-column box
+// (DRAM moves 64-byte granules anyway).  Heights 10..12 cover the floor flips of the coordinate
+// round trip.  One tensor map per (level, height).
 struct alignas(64) LookupTmaMaps {
-  CUtensorMap main[RAFTCORR_MAX_LEVELS][kBoxHeights];
-  CUtensorMap aux[RAFTCORR_MAX_LEVELS][kBoxHeights];
+  CUtensorMap m[RAFTCORR_MAX_LEVELS][kBoxHeights];
 };
 
 struct LookupTmaParams {
   LevelDev lv[RAFTCORR_MAX_LEVELS];
   const float* coords;
   float* out;
-  int B, H, W, mode, tiles_x;
+  int B, H, W, tiles_x;
   long long tiles;
 };
 
@@ -62,42 +61,21 @@ struct Cfg {
   static constexpr int kChannels = L * kRd2;
   static constexpr int kTaps = L * 2 * kRd;                      // tap coordinates per query
   static constexpr int kTapRounds = (kTaps + 31) / 32;
-  static constexpr int kIGroups = 3;                             // x taps per lane: i = ib + 3*ii
-  static constexpr int kIPer = (kRd + kIGroups - 1) / kIGroups;
-  static constexpr int kActive = kRd * kIGroups;                 // lanes with work (27 or 21)
+  static constexpr int kJGroups = 3;                             // lane = i * 3 + jb, j = 3 * jb + jj
+  static constexpr int kJPer = (kRd + kJGroups - 1) / kJGroups;
+  static constexpr int kActive = kRd * kJGroups;                 // lanes with work (27 or 21)
   static constexpr int kOffOut = kDepth * kWarpsTma * kWarpBufBytes;
   static constexpr int kOutBytes = ((kChannels * kOutPitch * 4 + 127) / 128) * 128;
-  static constexpr int kOffTab = kOffOut + kOutBytes;
-  static constexpr int kTabBytes = kWarpsTma * RAFTCORR_MAX_LEVELS * 2 * kMaxRd * 8;
-  static constexpr int kOffCoords = kOffTab + kTabBytes;         // [warp][depth] float2
-  static constexpr int kOffBars = kOffCoords + kWarpsTma * kDepth * 8;
+  static constexpr int kOffTab = kOffOut + kOutBytes;            // [warp][depth][kTabEntries] Tap
+  static constexpr int kTabBytes = kWarpsTma * kDepth * kTabEntries * 8;
+  static constexpr int kOffWin = kOffTab + kTabBytes;            // [warp][depth][L] int4
+  static constexpr int kWinBytes = kWarpsTma * kDepth * RAFTCORR_MAX_LEVELS * 16;
+  static constexpr int kOffBars = kOffWin + kWinBytes;
   static constexpr int kSmem = kOffBars + kWarpsTma * kDepth * 8;
 };
 
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
-
-// Window geometry of one (query, level), derived from the first and last tap of each axis.
-struct Window {
-  int x_lo, y_lo;   // floor index of tap -R per axis
-  int ox;           // x_lo - box start (0..3)
-  int hsel;         // box height - 10
-  bool need_aux;    // columns 12..15 of the box are touched
-  bool fast;        // window fits the staged boxes
-};
-
-__device__ __forceinline__ Window make_window(int x_lo, int x_last, int y_lo, int y_last) {
-  Window w;
-  const int wdt = x_last + 2 - x_lo, hgt = y_last + 2 - y_lo;
-  w.x_lo = x_lo;
-  w.y_lo = y_lo;
-  w.fast = (wdt >= 1) & (wdt <= kFoot) & (hgt >= 1) & (hgt <= kFoot);
-  w.ox = x_lo & 3;  // two's complement: also right for negative x_lo
-  w.need_aux = w.ox + wdt > kFoot;
-  const int h = hgt < 10 ? 10 : (hgt > 12 ? 12 : hgt);
-  w.hsel = h - 10;
-  return w;
 }
 
 // rare path: |coords| so large that fp32 spacing breaks the window; sample straight from global
@@ -108,7 +86,7 @@ __device__ __noinline__ float sample_direct(const LevelDev& lv, long long q, Tap
                           a.frac, c.frac);
 }
 
-template <int R, int L>
+template <int R, int L, int kMode>
 __global__ void __launch_bounds__(kThreadsTma, 1)
 lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_constant__ LookupTmaMaps maps) {
   using C = Cfg<R, L>;
@@ -117,8 +95,8 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
   const uint32_t smem_base = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* out_s = reinterpret_cast<float*>(smem + C::kOffOut);
-  Tap* tab = reinterpret_cast<Tap*>(smem + C::kOffTab) + warp * (RAFTCORR_MAX_LEVELS * 2 * kMaxRd);
-  float2* coords_w = reinterpret_cast<float2*>(smem + C::kOffCoords) + warp * kDepth;
+  Tap* tab_w = reinterpret_cast<Tap*>(smem + C::kOffTab) + warp * (kDepth * kTabEntries);
+  int4* win_w = reinterpret_cast<int4*>(smem + C::kOffWin) + warp * (kDepth * RAFTCORR_MAX_LEVELS);
   const uint32_t bar0 = smem_base + C::kOffBars + warp * kDepth * 8;   // this warp's mbarriers
 
   if (lane == 0) {
@@ -128,65 +106,30 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
   __syncthreads();
 
   const long long N = (long long)p.H * p.W;
-  const long long n_tiles = (p.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;  // tiles of this CTA
-  const long long n_units = 2 * n_tiles;
+  const int n_tiles = (int)((p.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);  // tiles of this CTA
 
-  // unit -> (b, y, x) of this warp's query
-  auto locate = [&](long long u, int& b, int& y, int& x) {
-    const long long tile = blockIdx.x + (u >> 1) * gridDim.x;
-    const int xt = (int)(tile % p.tiles_x);
-    y = (int)((tile / p.tiles_x) % p.H);
-    b = (int)(tile / ((long long)p.tiles_x * p.H));
-    x = xt * kTileQ + (int)(u & 1) * kUnitQ + warp;
+  // 32-bit tile arithmetic only (64-bit div/mod costs ~40 instructions each on the SM)
+  struct Cursor {
+    int b, y, x0;
+    bool live;
   };
-  auto load_coords = [&](long long u, float& cx, float& cy) {
-    int b, y, x;
-    cx = cy = 0.0f;
-    if (u < n_units) {
-      locate(u, b, y, x);
-      if (x < p.W) {
-        const long long pix = (long long)y * p.W + x;
-        cx = __ldg(p.coords + ((long long)b * 2 + 0) * N + pix);
-        cy = __ldg(p.coords + ((long long)b * 2 + 1) * N + pix);
-      }
-    }
+  auto cursor_at = [&](int k) {
+    Cursor c;
+    c.live = k < n_tiles;
+    const unsigned tile = blockIdx.x + (unsigned)(c.live ? k : 0) * gridDim.x;
+    const unsigned t2 = tile / (unsigned)p.tiles_x;
+    c.x0 = (int)(tile - t2 * (unsigned)p.tiles_x) * kTileQ;
+    c.b = (int)(t2 / (unsigned)p.H);
+    c.y = (int)(t2 - (unsigned)c.b * (unsigned)p.H);
+    return c;
   };
-  // issue the window loads of unit u into buffer u % kDepth
-  auto issue = [&](long long u, float cx, float cy) {
-    int b, y, x;
-    locate(u, b, y, x);
-    if (x >= p.W) return;
-    const int s = (int)(u % kDepth);
-    if (lane == 0) coords_w[s] = make_float2(cx, cy);
-    // lanes 0..4L-1: (level, {x first, x last, y first, y last}) tap floors
-    int fl = 0;
-    {
-      const int l = (lane >> 2) < L ? (lane >> 2) : 0;
-      const LevelDev& lv = p.lv[l];
-      const bool is_y = lane & 2;
-      const float c = __fmul_rn(is_y ? cy : cx, lv.inv_pow2);
-      fl = make_tap(c, (lane & 1) ? R : -R, is_y ? lv.sm1y : lv.sm1x, is_y ? lv.invy : lv.invx,
-                    is_y ? lv.halfy : lv.halfx, p.mode).i0;
-    }
-    const int l = lane < L ? lane : 0;
-    const Window w = make_window(__shfl_sync(0xffffffffu, fl, 4 * l), __shfl_sync(0xffffffffu, fl, 4 * l + 1),
-                                 __shfl_sync(0xffffffffu, fl, 4 * l + 2), __shfl_sync(0xffffffffu, fl, 4 * l + 3));
-    uint32_t bytes = lane < L ? (uint32_t)((10 + w.hsel) * (48 + (w.need_aux ? 16 : 0))) : 0u;
-    bytes += __shfl_xor_sync(0xffffffffu, bytes, 1);
-    bytes += __shfl_xor_sync(0xffffffffu, bytes, 2);
-    const uint32_t bar = bar0 + 8 * s;
-    if (lane == 0) mbar_expect_tx(bar, bytes);
-    __syncwarp();
-    if (lane < L) {
-      const LevelDev& lv = p.lv[lane];
-      // windows entirely outside the image are all zeros wherever the box sits
-      const int bx = max(-64, min(w.x_lo - w.ox, (lv.W + 64) & ~3));
-      const int by = max(-64, min(w.y_lo, lv.H + 64));
-      const int q = (int)((long long)b * N + (long long)y * p.W + x);
-      const uint32_t dst = smem_base + (s * kWarpsTma + warp) * kWarpBufBytes + lane * kSlotBytes;
-      tma_load_3d(dst, &maps.main[lane][w.hsel], bar, bx, by, q);
-      if (w.need_aux) tma_load_3d(dst + kAuxOff * 4, &maps.aux[lane][w.hsel], bar, bx + kFoot, by, q);
-    }
+  // lanes 0/1 fetch x/y of this warp's query in (tile cursor, half); 0 when it does not exist
+  auto load_coord = [&](const Cursor& c, int half) -> float {
+    float v = 0.0f;
+    const int x = c.x0 + half * kUnitQ + warp;
+    if (c.live && lane < 2 && x < p.W)
+      v = __ldg(p.coords + ((long long)c.b * 2 + lane) * N + (long long)c.y * p.W + x);
+    return v;
   };
 
   // per-lane description of the tap this lane evaluates in each round of the tap-table phase
@@ -210,90 +153,125 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
     t_isy[r] = axis;
     t_slot[r] = t < C::kTaps ? (l * 2 + axis) * kMaxRd + tap : -1;
   }
-  // sampling phase: lane = j * 3 + ib handles y tap j and x taps i = ib + 3 * ii
-  const int tj = lane / C::kIGroups;
-  const int tib = lane - tj * C::kIGroups;
 
-  {  // prologue: two units in flight
-    float cx, cy;
-    for (int u = 0; u < 2; ++u)
-      if (u < n_units) {
-        load_coords(u, cx, cy);
-        issue(u, cx, cy);
-      }
-  }
-  float ncx, ncy;
-  load_coords(2, ncx, ncy);
-  uint32_t phases = 0;  // bit s = parity of the next completion of this warp's buffer s
-
-  for (long long u = 0; u < n_units; ++u) {
-    if (u + 2 < n_units) issue(u + 2, ncx, ncy);
-    load_coords(u + 3, ncx, ncy);
-
-    int b, y, x;
-    locate(u, b, y, x);
-    const int s = (int)(u % kDepth);
-    const int qi = (int)(u & 1) * kUnitQ + warp;
-    if (x < p.W) {
-      mbar_wait(bar0 + 8 * s, (phases >> s) & 1u, 2);
-      phases ^= 1u << s;
-      const float2 cxy = coords_w[s];
+  // Stage one unit: tap table -> window geometry -> one TMA box per level into ring slot s.
+  auto stage = [&](const Cursor& c, int half, int s, float cmine) {
+    const int x = c.x0 + half * kUnitQ + warp;
+    if (!c.live || x >= p.W) return;
+    const float cx = __shfl_sync(0xffffffffu, cmine, 0), cy = __shfl_sync(0xffffffffu, cmine, 1);
+    Tap* tab = tab_w + s * kTabEntries;
 #pragma unroll
-      for (int r = 0; r < C::kTapRounds; ++r) {
-        if (t_slot[r] >= 0) {
-          const float c = __fmul_rn(t_isy[r] ? cxy.y : cxy.x, t_pow[r]);
-          tab[t_slot[r]] = make_tap(c, t_off[r], t_sm1[r], t_inv[r], t_half[r], p.mode);
-        }
-      }
-      __syncwarp();
-      const float* buf = reinterpret_cast<const float*>(smem + (s * kWarpsTma + warp) * kWarpBufBytes);
+    for (int r = 0; r < C::kTapRounds; ++r)
+      if (t_slot[r] >= 0)
+        tab[t_slot[r]] = make_tap(__fmul_rn(t_isy[r] ? cy : cx, t_pow[r]), t_off[r], t_sm1[r], t_inv[r],
+                                  t_half[r], kMode);
+    __syncwarp();
+    if (lane < L) {
+      const Tap* tx = tab + (lane * 2 + 0) * kMaxRd;
+      const Tap* ty = tab + (lane * 2 + 1) * kMaxRd;
+      const int x_lo = tx[0].i0, y_lo = ty[0].i0;
+      const int wdt = tx[rd - 1].i0 + 2 - x_lo, hgt = ty[rd - 1].i0 + 2 - y_lo;
+      const int fast = (wdt >= 1) & (wdt <= kFoot) & (hgt >= 1) & (hgt <= kFoot);
+      const int h = hgt < 10 ? 10 : (hgt > 12 ? 12 : hgt);
+      // .x: box column of a tap with floor index i0 is (i0 + .x); .y: first row; .z: box height; .w: fast
+      win_w[s * RAFTCORR_MAX_LEVELS + lane] = make_int4((x_lo & 3) - x_lo, y_lo, h, fast);
+    }
+    __syncwarp();
+    if (lane == 0) {
+      const uint32_t bar = bar0 + 8 * s;
+      const int q = (int)((long long)c.b * N + (long long)c.y * p.W + x);
+      const uint32_t dst = smem_base + (s * kWarpsTma + warp) * kWarpBufBytes;
+      int4 w[L];
+      uint32_t bytes = 0;
 #pragma unroll
       for (int l = 0; l < L; ++l) {
-        const Tap* tx = tab + (l * 2 + 0) * kMaxRd;
-        const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
-        const Window w = make_window(tx[0].i0, tx[rd - 1].i0, ty[0].i0, ty[rd - 1].i0);
-        if (lane < C::kActive) {
-          const Tap c = ty[tj];
-          const float* f = buf + l * (kSlotBytes / 4);
-          const int r0 = (c.i0 - w.y_lo) * kFoot;        // main row offset; aux rows have pitch 4
-          float* o = out_s + (l * rd2 + tj) * kOutPitch + qi;
+        w[l] = win_w[s * RAFTCORR_MAX_LEVELS + l];
+        bytes += (uint32_t)(w[l].z * kBoxW * 4);
+      }
+      mbar_expect_tx(bar, bytes);
 #pragma unroll
-          for (int ii = 0; ii < C::kIPer; ++ii) {
-            const int i = tib + C::kIGroups * ii;
-            if (i < rd) {
-              const Tap a = tx[i];
-              float v;
-              if (w.fast) {
-                const int c0 = w.ox + (a.i0 - w.x_lo), c1 = c0 + 1;   // box columns of the two corners
-                const int o0 = c0 < kFoot ? r0 + c0 : kAuxOff + (r0 / 3) + (c0 - kFoot);
-                const int o1 = c1 < kFoot ? r0 + c1 : kAuxOff + (r0 / 3) + (c1 - kFoot);
-                const int d0 = c0 < kFoot ? kFoot : 4, d1 = c1 < kFoot ? kFoot : 4;
-                v = bilinear_combine(f[o0], f[o1], f[o0 + d0], f[o1 + d1], a.frac, c.frac);
-              } else {
-                v = sample_direct(p.lv[l], (long long)b * N + (long long)y * p.W + x, a, c);
+      for (int l = 0; l < L; ++l) {
+        // box start = x_lo & ~3 = -(w.x); windows entirely outside the image are all zeros
+        // wherever the box sits, so far-away origins are clamped to keep the coordinates sane
+        const int bx = max(-64, min(-w[l].x, (p.lv[l].W + 64) & ~3));
+        const int by = max(-64, min(w[l].y, p.lv[l].H + 64));
+        const CUtensorMap* m = w[l].z == 10 ? &maps.m[l][0] : (w[l].z == 11 ? &maps.m[l][1] : &maps.m[l][2]);
+        tma_load_3d(dst + l * kSlotBytes, m, bar, bx, by, q);
+      }
+    }
+  };
+
+  // sampling phase: lane = i * 3 + jb handles x tap i and y taps j = 3 * jb + jj
+  const int ti = lane / C::kJGroups;
+  const int tj0 = (lane - ti * C::kJGroups) * C::kJPer;
+
+  Cursor cur = cursor_at(0), nxt = cursor_at(1), nxt2 = cursor_at(2);
+  stage(cur, 0, 0, load_coord(cur, 0));   // prologue: two units in flight
+  stage(cur, 1, 1, load_coord(cur, 1));
+  float cnext = load_coord(nxt, 0);       // coordinates are fetched one unit ahead of staging
+  uint32_t phases = 0;                    // bit s = parity of the next completion of ring slot s
+  int slot = 0;                           // ring slot of the unit being sampled
+
+  for (int k = 0; k < n_tiles; ++k) {
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      {
+        int s2 = slot + 2;
+        s2 = s2 >= kDepth ? s2 - kDepth : s2;
+        stage(nxt, half, s2, cnext);      // unit two ahead: same half of the next tile
+        cnext = half == 0 ? load_coord(nxt, 1) : load_coord(nxt2, 0);
+      }
+      const int x = cur.x0 + half * kUnitQ + warp;
+      const int qi = half * kUnitQ + warp;
+      if (x < p.W) {
+        mbar_wait(bar0 + 8 * slot, (phases >> slot) & 1u, 2);
+        phases ^= 1u << slot;
+        if (lane < C::kActive) {
+          const Tap* tab = tab_w + slot * kTabEntries;
+          const float* buf = reinterpret_cast<const float*>(smem + (slot * kWarpsTma + warp) * kWarpBufBytes);
+#pragma unroll
+          for (int l = 0; l < L; ++l) {
+            const int4 w = win_w[slot * RAFTCORR_MAX_LEVELS + l];
+            const Tap a = tab[(l * 2 + 0) * kMaxRd + ti];
+            const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
+            const float* f = buf + l * (kSlotBytes / 4) + (a.i0 + w.x);
+            float* o = out_s + (l * rd2 + ti * rd) * kOutPitch + qi;
+#pragma unroll
+            for (int jj = 0; jj < C::kJPer; ++jj) {
+              const int j = tj0 + jj;
+              if (j < rd) {
+                const Tap c = ty[j];
+                float v;
+                if (w.w) {
+                  const float* g = f + (c.i0 - w.y) * kBoxW;
+                  v = bilinear_combine(g[0], g[1], g[kBoxW], g[kBoxW + 1], a.frac, c.frac);
+                } else {
+                  v = sample_direct(p.lv[l], (long long)cur.b * N + (long long)cur.y * p.W + x, a, c);
+                }
+                o[j * kOutPitch] = v;
               }
-              o[i * rd * kOutPitch] = v;
             }
           }
         }
       }
-    }
-    if (u & 1) {  // both halves of the output tile are in shared memory: write it out
       __syncwarp();
-      named_bar_sync(1, kThreadsTma);
-      const long long tile = blockIdx.x + (u >> 1) * gridDim.x;
-      const int x0 = (int)(tile % p.tiles_x) * kTileQ;
-      const int xx = x0 + lane;
+      slot = slot + 1 == kDepth ? 0 : slot + 1;
+    }
+    // both halves of the output tile are in shared memory: write it out as 128-byte rows
+    named_bar_sync(1, kThreadsTma);
+    {
+      const int xx = cur.x0 + lane;
       if (xx < p.W) {
-        float* dst = p.out + (long long)b * C::kChannels * N + (long long)y * p.W + xx;
+        float* dst = p.out + (long long)cur.b * C::kChannels * N + (long long)cur.y * p.W + xx;
 #pragma unroll 4
         for (int c = warp; c < C::kChannels; c += kWarpsTma)
           __stcs(dst + (long long)c * N, out_s[c * kOutPitch + lane]);
       }
-      named_bar_sync(1, kThreadsTma);
-    } else {
-      __syncwarp();
     }
+    named_bar_sync(1, kThreadsTma);
+    cur = nxt;
+    nxt = nxt2;
+    nxt2 = cursor_at(k + 3);
   }
 }
 
@@ -345,7 +323,7 @@ bool tma_eligible(const raftcorr_level* levels, int L, int r) {
   return get_encode() != nullptr;
 }
 
-template <int R, int L>
+template <int R, int L, int kMode>
 int launch_tma(const LookupTmaParams& p, const LookupTmaMaps& maps, cudaStream_t stream) {
   using C = Cfg<R, L>;
   int dev = 0;
@@ -353,12 +331,12 @@ int launch_tma(const LookupTmaParams& p, const LookupTmaMaps& maps, cudaStream_t
   static std::atomic<int> sm_count[64];  // per device: 0 = kernel attribute not set yet
   int sms = (dev >= 0 && dev < 64) ? sm_count[dev].load(std::memory_order_acquire) : 0;
   if (sms == 0) {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(lookup_fwd_tma_kernel<R, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
+    RC_CHECK_CUDA(cudaFuncSetAttribute(lookup_fwd_tma_kernel<R, L, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
     RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (dev >= 0 && dev < 64) sm_count[dev].store(sms, std::memory_order_release);
   }
   const int grid = (int)(p.tiles < sms ? p.tiles : sms);
-  lookup_fwd_tma_kernel<R, L><<<grid, kThreadsTma, C::kSmem, stream>>>(p, maps);
+  lookup_fwd_tma_kernel<R, L, kMode><<<grid, kThreadsTma, C::kSmem, stream>>>(p, maps);
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -401,13 +379,9 @@ int launch_lookup_fwd_tma(const raftcorr_level* levels, int L, const float* coor
       cuuint64_t dims[3] = {(cuuint64_t)levels[l].W, (cuuint64_t)levels[l].H, (cuuint64_t)BN};
       cuuint64_t strides[2] = {(cuuint64_t)levels[l].pitch * 4, (cuuint64_t)levels[l].image_stride * 4};
       for (int h = 0; h < kBoxHeights; ++h) {
-        cuuint32_t box[3] = {(cuuint32_t)kFoot, (cuuint32_t)(10 + h), 1};
-        if (int rc = encode(&maps.main[l][h], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, levels[l].data, dims, strides,
+        cuuint32_t box[3] = {(cuuint32_t)kBoxW, (cuuint32_t)(10 + h), 1};
+        if (int rc = encode(&maps.m[l][h], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, levels[l].data, dims, strides,
                             box, CU_TENSOR_MAP_SWIZZLE_NONE, "lookup window", CU_TENSOR_MAP_L2_PROMOTION_NONE))
-          return rc;
-        box[0] = 4;
-        if (int rc = encode(&maps.aux[l][h], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, levels[l].data, dims, strides,
-                            box, CU_TENSOR_MAP_SWIZZLE_NONE, "lookup window tail", CU_TENSOR_MAP_L2_PROMOTION_NONE))
           return rc;
       }
     }
@@ -418,11 +392,17 @@ int launch_lookup_fwd_tma(const raftcorr_level* levels, int L, const float* coor
   p.B = B;
   p.H = H;
   p.W = W;
-  p.mode = mode;
   p.tiles_x = (W + kTileQ - 1) / kTileQ;
   p.tiles = (long long)B * H * p.tiles_x;
   if (p.tiles == 0) return 0;
-  return r == 4 ? launch_tma<4, 4>(p, maps, stream) : launch_tma<3, 4>(p, maps, stream);
+  switch (mode * 8 + r) {
+    case RAFTCORR_COORD_ATEN_CPU * 8 + 4: return launch_tma<4, 4, RAFTCORR_COORD_ATEN_CPU>(p, maps, stream);
+    case RAFTCORR_COORD_ATEN_CPU * 8 + 3: return launch_tma<3, 4, RAFTCORR_COORD_ATEN_CPU>(p, maps, stream);
+    case RAFTCORR_COORD_ATEN_CUDA * 8 + 4: return launch_tma<4, 4, RAFTCORR_COORD_ATEN_CUDA>(p, maps, stream);
+    case RAFTCORR_COORD_ATEN_CUDA * 8 + 3: return launch_tma<3, 4, RAFTCORR_COORD_ATEN_CUDA>(p, maps, stream);
+    case RAFTCORR_COORD_DIRECT * 8 + 4: return launch_tma<4, 4, RAFTCORR_COORD_DIRECT>(p, maps, stream);
+    default: return launch_tma<3, 4, RAFTCORR_COORD_DIRECT>(p, maps, stream);
+  }
 }
 
 }  // namespace raftcorr
