@@ -1,0 +1,320 @@
+"""bench.py — RAFT frame-pairs/s at 440x1024, 12 iterations (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+One "step" = one RAFT inference (12 refinement iterations) over a batch of 8 synthetic frame
+pairs per GPU: stock PyTorch/cuDNN encoders + update block (harness/raft_stock.py, random-init
+weights) around THIS repo's correlation path (pytorch-raft_b200/corr.py -> libraftcorr_b200.so).
+Frame pairs shard by batch across GPUs: no collective on the data path ("scaling": "weak").
+
+  value      whole-job frame-pairs/s with the frames already resident in HBM (CUDA events,
+             barrier + synchronize on both sides, max over ranks)
+  e2e        the same through the public API with HOST frames: pinned host -> device copy of
+             both frames and device -> host read of the full-resolution flow inside the timed
+             region, every step
+  roofline   the lookup kernel (the path's dominant kernel, 12 launches per step): algorithmic
+             bytes (2904 B/query) / its CUDA-event duration measured live inside
+             the timed region, against the measured HBM peak in MEASURED_PEAKS.json
+  cpu_baseline / --impl reference
+             the reference's CPU implementation of the path (oracle/torch_restatement.py issues
+             the same ATen ops as core/corr.py; /root/reference itself cannot travel) inside the
+             same harness model on the box's host cores, on a bounded sample (1 pair per step)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "pytorch-raft_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+METRIC = "RAFT frame-pairs/s @440x1024 12 iters; corr lookup HBM GB/s vs peak"
+UNIT = "frame-pairs/s"
+IMG_H, IMG_W, ITERS, BATCH_PER_GPU = 440, 1024, 12, 8
+RADIUS, LEVELS = 4, 4
+LOOKUP_BYTES_PER_QUERY = LEVELS * (2 * RADIUS + 2) ** 2 * 4 + 8 + LEVELS * (2 * RADIUS + 1) ** 2 * 4  # 2904
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def ncu_traffic_per_launch():
+    """dram read+write bytes per lookup launch from the committed ncu --set full capture."""
+    path = os.path.join(ROOT, "profiles", "lookup_traffic.json")
+    if os.path.exists(path):
+        try:
+            d = json.load(open(path))
+            if d.get("workload") == "cfg2_b8_55x128":
+                return float(d["dram_bytes_per_launch"])
+        except Exception:
+            pass
+    return None
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+        self.t0 = self.t1 = None   # the timed window (perf_counter); samples outside are dropped
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-i", str(self.index), "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        sm, mx, reasons = [], 0, set()
+        for stamp, r in self.rows:
+            if self.t0 is not None and not (self.t0 <= stamp <= (self.t1 or stamp)):
+                continue
+            try:
+                sm.append(int(float(r[0])))
+                mx = max(mx, int(float(r[1])))
+            except (ValueError, IndexError):
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_model(device):
+    from harness.raft_stock import StockRAFT
+    torch.manual_seed(1234)
+    return StockRAFT().eval().to(device)
+
+
+def synthetic_frames(batch, seed, pin=False):
+    gen = torch.Generator().manual_seed(seed)
+    a = torch.rand(batch, 3, IMG_H, IMG_W, generator=gen) * 255.0
+    b = torch.rand(batch, 3, IMG_H, IMG_W, generator=gen) * 255.0
+    return (a.pin_memory(), b.pin_memory()) if pin else (a, b)
+
+
+# ------------------------------------------------------------------------------------------------
+def run_cpu_reference(steps: int, warmup: int, sample_pairs: int = 1):
+    """The reference's CPU implementation of the path inside the harness model, on host cores."""
+    from oracle import torch_restatement as tr
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    model = make_model("cpu")
+    im1, im2 = synthetic_frames(sample_pairs, seed=99)
+    factory = lambda f1, f2, r: tr.TorchCorrBlock(f1, f2, LEVELS, r)  # noqa: E731
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            model(im1, im2, factory, iters=ITERS)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+    total = sum(times)
+    return {"value": sample_pairs * len(times) / total, "ms_per_step": 1e3 * total / len(times),
+            "cores": threads, "kind": "port",
+            "sample": f"{sample_pairs} frame pair(s) per step at 440x1024, 12 iterations, fp32, {len(times)} timed step(s); "
+                      "oracle/torch_restatement.py (same ATen ops as core/corr.py) inside harness/raft_stock.py"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=None, help="bf16 (default) | tf32 | fp32 for the volume build")
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    base_config = {"workload": "RAFT inference, Sintel shape 440x1024 (55x128 fmaps), 12 iters, "
+                               f"batch {BATCH_PER_GPU} per GPU, random-init weights",
+                   "image": [IMG_H, IMG_W], "iters": ITERS, "batch_per_gpu": BATCH_PER_GPU,
+                   "corr": "CorrBlock 4 levels r=4", "sharding": f"batch x{max(world, args.gpus)}, no collective"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        ref = run_cpu_reference(args.steps, warmup)
+        line = {"impl": "reference", "metric": METRIC, "value": ref["value"], "unit": UNIT, "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": warmup, "ms_per_step": ref["ms_per_step"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": dict(base_config, batch_per_step=1, where="host CPU"),
+                "cpu_baseline": {"value": ref["value"], "unit": UNIT, "cores": ref["cores"], "kind": ref["kind"],
+                                 "sample": ref["sample"]},
+                "e2e": {"value": ref["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+
+    assert torch.cuda.is_available(), "bench.py (impl ours) needs CUDA devices; there is no CPU fallback"
+    import corr as raftcorr_dropin  # the drop-in module; raises if libraftcorr_b200.so is missing
+
+    distributed = world > 1
+    if distributed:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank if distributed else 0)
+    torch.cuda.set_device(dev)
+
+    model = make_model(dev)
+    host1, host2 = synthetic_frames(BATCH_PER_GPU, seed=100 + rank, pin=True)
+    dev1, dev2 = host1.to(dev), host2.to(dev)
+    host_flow = torch.empty(BATCH_PER_GPU, 2, IMG_H, IMG_W).pin_memory()
+    factory = lambda f1, f2, r: raftcorr_dropin.CorrBlock(f1, f2, num_levels=LEVELS, radius=r,  # noqa: E731
+                                                          precision=args.precision)
+
+    lookup_events = []
+
+    def timed_lookup(corr_fn, coords):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = corr_fn(coords)
+        b.record()
+        lookup_events.append((a, b))
+        return out
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident(hook=None):
+        with torch.no_grad():
+            return model(dev1, dev2, factory, iters=ITERS, lookup_hook=hook)[1]
+
+    def step_e2e():
+        with torch.no_grad():
+            a = host1.to(dev, non_blocking=True)
+            b = host2.to(dev, non_blocking=True)
+            flow = model(a, b, factory, iters=ITERS)[1]
+            host_flow.copy_(flow, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return host_flow
+
+    for _ in range(warmup):
+        step_resident()
+    step_e2e()
+
+    def timed(fn, steps):
+        barrier()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(steps):
+            fn()
+        t1.record()
+        barrier()
+        ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
+        if distributed:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    sampler = ClockSampler(dev.index or 0)
+    if rank == 0:
+        sampler.start()          # nvidia-smi needs a moment to start: launch it before warm-up ends
+        for _ in range(2):
+            step_resident()
+        sampler.t0 = time.perf_counter()
+    ms_total = timed(lambda: step_resident(timed_lookup), args.steps)
+    if rank == 0:
+        sampler.t1 = time.perf_counter()
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e = timed(step_e2e, args.steps)
+
+    # kernel shares: the build (pack x2 + tcgen05 GEMM) once per step, timed on its own
+    fm = torch.randn(BATCH_PER_GPU, 256, IMG_H // 8, IMG_W // 8, device=dev)
+    fm2 = torch.randn_like(fm)
+    from raftcorr_b200 import ops
+    for _ in range(2):
+        ops.build_pyramid(fm, fm2, LEVELS, args.precision)
+    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    b0.record()
+    for _ in range(5):
+        ops.build_pyramid(fm, fm2, LEVELS, args.precision)
+    b1.record()
+    torch.cuda.synchronize()
+    build_ms = b0.elapsed_time(b1) / 5
+
+    if rank != 0:
+        if distributed:
+            dist.destroy_process_group()
+        return
+
+    n_gpus = world if distributed else 1
+    pairs = BATCH_PER_GPU * n_gpus * args.steps
+    lookup_ms = [a.elapsed_time(b) for a, b in lookup_events]
+    lookup_avg_ms = sum(lookup_ms) / max(len(lookup_ms), 1)
+    queries = BATCH_PER_GPU * (IMG_H // 8) * (IMG_W // 8)
+    peak, peak_src = measured_peaks()
+    achieved = queries * LOOKUP_BYTES_PER_QUERY / (lookup_avg_ms * 1e-3) / 1e9
+    h2d = 2 * BATCH_PER_GPU * 3 * IMG_H * IMG_W * 4
+    d2h = BATCH_PER_GPU * 2 * IMG_H * IMG_W * 4
+
+    line = {
+        "metric": METRIC, "value": pairs / (ms_total * 1e-3), "unit": UNIT, "n_gpus": n_gpus,
+        "steps": args.steps, "warmup": warmup, "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16" if args.precision in (None, "bf16") else args.precision,
+        "data": "synthetic",
+        "config": dict(base_config, l2="inputs exceed L2 (2.1 GB pyramid + 115 MB frames per step)",
+                       build_precision=args.precision or "bf16", encoders="stock PyTorch/cuDNN fp32"),
+        "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": (3 + ITERS) * args.steps * n_gpus,
+        "roofline": {"kernel": "lookup_fwd_tma_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic_per_launch(),
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": queries * LOOKUP_BYTES_PER_QUERY,
+                     "launch_us": lookup_avg_ms * 1e3, "launches_timed": len(lookup_ms)},
+        "kernels": {"lookup_us": lookup_avg_ms * 1e3, "build_ms": build_ms,
+                    "corr_path_ms_per_step": build_ms + ITERS * lookup_avg_ms,
+                    "corr_path_share_of_step": (build_ms + ITERS * lookup_avg_ms) / (ms_total / args.steps)},
+        "clocks": clocks,
+    }
+    if not args.skip_cpu_baseline and n_gpus == 1:
+        ref = run_cpu_reference(steps=1, warmup=1)
+        line["cpu_baseline"] = {"value": ref["value"], "unit": UNIT, "cores": ref["cores"], "kind": ref["kind"],
+                                "sample": ref["sample"]}
+    print(json.dumps(line))
+    if distributed:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -38,6 +38,19 @@ __device__ __forceinline__ Tap make_tap(float centre, int tap_offset, float sm1,
   return t;
 }
 
+// make_tap with the FMA division and a branch-free floor (NaN -> far outside, range clamped)
+__device__ __forceinline__ Tap make_tap_fast(float centre, int tap_offset, float sm1, float inv,
+                                             float half, int mode) {
+  const float p = __fadd_rn(centre, (float)tap_offset);
+  const float idx = sample_index_fast(p, sm1, inv, half, mode);
+  const float fl = floorf(idx);
+  Tap t;
+  const int i = __float2int_rd(fl);  // saturating conversion
+  t.i0 = (fl == fl) ? max(-(1 << 29), min(i, 1 << 29)) : -(1 << 29);
+  t.frac = __fsub_rn(idx, fl);
+  return t;
+}
+
 __device__ __forceinline__ float load_pixel(const float* img, const LevelDev& lv, int gy, int gx) {
   const bool ok = (gy >= 0) & (gy < lv.H) & (gx >= 0) & (gx < lv.W);
   return ok ? __ldg(img + (long long)gy * lv.pitch + gx) : 0.0f;

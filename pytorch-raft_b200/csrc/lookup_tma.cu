@@ -163,7 +163,7 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
 #pragma unroll
     for (int r = 0; r < C::kTapRounds; ++r)
       if (t_slot[r] >= 0)
-        tab[t_slot[r]] = make_tap(__fmul_rn(t_isy[r] ? cy : cx, t_pow[r]), t_off[r], t_sm1[r], t_inv[r],
+        tab[t_slot[r]] = make_tap_fast(__fmul_rn(t_isy[r] ? cy : cx, t_pow[r]), t_off[r], t_sm1[r], t_inv[r],
                                   t_half[r], kMode);
     __syncwarp();
     if (lane < L) {
@@ -177,7 +177,7 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
       win_w[s * RAFTCORR_MAX_LEVELS + lane] = make_int4((x_lo & 3) - x_lo, y_lo, h, fast);
     }
     __syncwarp();
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t bar = bar0 + 8 * s;
       const int q = (int)((long long)c.b * N + (long long)c.y * p.W + x);
       const uint32_t dst = smem_base + (s * kWarpsTma + warp) * kWarpBufBytes;
