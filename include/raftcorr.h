@@ -73,6 +73,25 @@ int raftcorr_build_pyramid(const float* fmap1, const float* fmap2, int B, int D,
                            int num_levels, const raftcorr_level* levels, int precision,
                            void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Same result as raftcorr_build_pyramid at RAFTCORR_PREC_BF16 / RAFTCORR_PREC_TF32, for callers that
+ * cannot hand over a workspace.  This entry point has no counterpart in the reference.
+ * Who needs it: a host that claims the whole device for its own pool at start-up and passes a
+ * plug-in only input/output pointers (the binding has no way to ask that pool for more), or a
+ * real-time loop that bans cudaMalloc/cudaFree because they stall the device.  The packed
+ * operands (2 * B*H*W*D elements of 2 or 4 bytes, each half rounded up to 256 B) go into a fixed
+ * RAFTCORR_NOALLOC_SCRATCH_BYTES array inside the library image: every GPU that loads the library
+ * holds that memory until the process ends.  Larger problems are refused with
+ * RAFTCORR_E_WORKSPACE.  It calls no cudaMalloc/cudaFree and no allocating library routine.
+ *  - The first call on each device looks the array's device address up; make that first call
+ *    before starting any stream capture.
+ *  - All calls on a device share the one array.  Each call fully rewrites the part it reads, so
+ *    stale contents are harmless, but two calls whose kernels overlap on the GPU (different
+ *    streams, or different host threads on the same device) race on it: serialise them. */
+#define RAFTCORR_NOALLOC_SCRATCH_BYTES (8u << 20)
+int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B, int D, int H, int W,
+                                   int num_levels, const raftcorr_level* levels, int precision,
+                                   void* stream);
+
 /* ---- (2) 4-level (2r+1)^2 bilinear window lookup: replaces CorrBlock.__call__
  *      (core/corr.py:29-50) including bilinear_sampler (core/utils/utils.py:57-65) and
  *      grid_sample(align_corners=True, zero padding).

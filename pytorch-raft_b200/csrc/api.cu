@@ -40,6 +40,8 @@ int64_t build_tc_workspace_bytes(int B, int D, int H, int W, int precision);
 int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W, int L,
                     const raftcorr_level* levels, int precision, void* ws, int64_t ws_bytes,
                     cudaStream_t stream);
+int launch_build_tc_noalloc(const float* f1, const float* f2, int B, int D, int H, int W, int L,
+                            const raftcorr_level* levels, int precision, cudaStream_t stream);
 int64_t build_bwd_workspace_bytes(int B, int D, int H, int W);
 int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, const float* f2,
                      float* g1, float* g2, int B, int D, int H, int W, void* ws, int64_t ws_bytes,
@@ -116,6 +118,21 @@ int raftcorr_build_pyramid(const float* fmap1, const float* fmap2, int B, int D,
              "build_pyramid: unknown precision %d", precision);
   return launch_build_tc(fmap1, fmap2, B, D, H, W, num_levels, levels, precision, workspace,
                          workspace_bytes, (cudaStream_t)stream);
+}
+
+int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B, int D, int H, int W,
+                                   int num_levels, const raftcorr_level* levels, int precision,
+                                   void* stream) {
+  RC_REQUIRE(fmap1 && fmap2, "build_pyramid_noalloc: fmap pointer is NULL");
+  RC_REQUIRE(B >= 0 && D >= 1 && H >= 1 && W >= 1, "build_pyramid_noalloc: bad sizes B=%d D=%d H=%d W=%d",
+             B, D, H, W);
+  RC_REQUIRE((long long)H * W <= (1 << 24), "build_pyramid_noalloc: fmap too large");
+  RC_REQUIRE(precision == RAFTCORR_PREC_BF16 || precision == RAFTCORR_PREC_TF32,
+             "build_pyramid_noalloc: precision must be RAFTCORR_PREC_BF16 or RAFTCORR_PREC_TF32 "
+             "(the fp32 build needs no workspace: call raftcorr_build_pyramid)");
+  if (int rc = check_levels(levels, num_levels, H, W, "build_pyramid_noalloc")) return rc;
+  return launch_build_tc_noalloc(fmap1, fmap2, B, D, H, W, num_levels, levels, precision,
+                                 (cudaStream_t)stream);
 }
 
 int raftcorr_lookup_fwd(const raftcorr_level* levels, int num_levels, const float* coords,

@@ -17,6 +17,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "tma_util.cuh"
 
@@ -403,6 +405,66 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   }
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of the tensor-core build.
+//
+// launch_build_tc() packs both feature maps into a caller-supplied workspace.  Some integrations
+// cannot supply one: a host application that gives the whole device to its own memory pool at
+// start-up and hands a plug-in nothing but raw input/output pointers (a ctypes / JNI / cgo
+// binding has no handle on the host's caching allocator), or a latency-critical loop whose
+// rules forbid cudaMalloc/cudaFree because those calls synchronise the device.  For them the
+// packed operands live in the fixed array below, which is part of the loaded library image:
+// every GPU that loads libraftcorr_b200.so holds these RAFTCORR_NOALLOC_SCRATCH_BYTES until the
+// process exits, whether or not the entry point is ever called.
+//
+// g_noalloc_scratch is a device symbol.  In host code its name is only a host-side stand-in, not
+// a device address, so the address is looked up once per device with cudaGetSymbolAddress (with
+// that device current) and that pointer is what the kernels and tensor maps receive.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RAFTCORR_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kMaxDevices] = {};   // device address of g_noalloc_scratch, per device
+
+// First use on a device performs the symbol lookup (which may initialise the module on that
+// device): make that first call outside any stream capture.
+int noalloc_scratch_for_current_device(void** out) {
+  int dev = -1;
+  RC_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(RAFTCORR_E_UNSUPPORTED, "build_pyramid_noalloc: device %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    const cudaError_t err = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (err != cudaSuccess) return cuda_fail(err, "cudaGetSymbolAddress(g_noalloc_scratch)");
+    if (ptr == nullptr) return fail(RAFTCORR_E_DRIVER, "build_pyramid_noalloc: scratch symbol has no device address");
+    g_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+int launch_build_tc_noalloc(const float* f1, const float* f2, int B, int D, int H, int W, int L,
+                            const raftcorr_level* levels, int precision, cudaStream_t stream) {
+  const int64_t need = build_tc_workspace_bytes(B, D, H, W, precision);
+  if (need > (int64_t)RAFTCORR_NOALLOC_SCRATCH_BYTES)
+    return fail(RAFTCORR_E_WORKSPACE,
+                "build_pyramid_noalloc: B=%d D=%d H=%d W=%d needs %lld B of packed operands, the built-in "
+                "scratch holds %lld B; use raftcorr_build_pyramid with a caller workspace",
+                B, D, H, W, (long long)need, (long long)RAFTCORR_NOALLOC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  if (int rc = noalloc_scratch_for_current_device(&scratch)) return rc;
+  // The pack kernels overwrite every byte of the scratch that the GEMM reads (rows beyond D or
+  // N are produced by TMA zero fill, not read from memory), so nothing has to be cleared between
+  // calls even though the array still holds the previous call's operands.
+  return launch_build_tc(f1, f2, B, D, H, W, L, levels, precision, scratch, RAFTCORR_NOALLOC_SCRATCH_BYTES, stream);
 }
 
 }  // namespace raftcorr

@@ -15,6 +15,7 @@ LIB_PATH = os.environ.get("RAFTCORR_LIB", os.path.join(PKG, "libraftcorr_b200.so
 MAX_LEVELS = 4
 COORD_ATEN_CPU, COORD_ATEN_CUDA, COORD_DIRECT = 0, 1, 2
 PREC_FP32, PREC_BF16, PREC_TF32 = 0, 1, 2
+NOALLOC_SCRATCH_BYTES = 8 << 20  # RAFTCORR_NOALLOC_SCRATCH_BYTES
 
 c_float_p = ctypes.c_void_p  # device pointers travel as integers
 
@@ -37,6 +38,8 @@ SIGNATURES = {
     "raftcorr_build_pyramid": (ctypes.c_int, [c_float_p, c_float_p] + [ctypes.c_int] * 5 +
                                [ctypes.POINTER(Level), ctypes.c_int, ctypes.c_void_p, ctypes.c_int64,
                                 ctypes.c_void_p]),
+    "raftcorr_build_pyramid_noalloc": (ctypes.c_int, [c_float_p, c_float_p] + [ctypes.c_int] * 5 +
+                                       [ctypes.POINTER(Level), ctypes.c_int, ctypes.c_void_p]),
     "raftcorr_lookup_fwd": (ctypes.c_int, [ctypes.POINTER(Level), ctypes.c_int, c_float_p, c_float_p] +
                             [ctypes.c_int] * 5 + [ctypes.c_void_p]),
     "raftcorr_lookup_bwd": (ctypes.c_int, [ctypes.POINTER(Level), ctypes.POINTER(Level), ctypes.c_int,
