@@ -252,7 +252,12 @@ def main():
         for _ in range(2):
             step_resident()
         sampler.t0 = time.perf_counter()
+    profile_range = bool(os.environ.get("BENCH_CUDA_PROFILER_RANGE"))  # ncu --profile-from-start off
+    if profile_range:
+        torch.cuda.profiler.start()
     ms_total = timed(lambda: step_resident(timed_lookup), args.steps)
+    if profile_range:
+        torch.cuda.profiler.stop()
     if rank == 0:
         sampler.t1 = time.perf_counter()
     clocks = sampler.stop() if rank == 0 else None
