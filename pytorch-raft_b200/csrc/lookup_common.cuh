@@ -39,9 +39,9 @@ __device__ __forceinline__ Tap make_tap(float centre, int tap_offset, float sm1,
 }
 
 // make_tap with the FMA division and a branch-free floor (NaN -> far outside, range clamped)
-__device__ __forceinline__ Tap make_tap_fast(float centre, int tap_offset, float sm1, float inv,
+__device__ __forceinline__ Tap make_tap_fast(float centre, float tap_offset, float sm1, float inv,
                                              float half, int mode) {
-  const float p = __fadd_rn(centre, (float)tap_offset);
+  const float p = __fadd_rn(centre, tap_offset);
   const float idx = sample_index_fast(p, sm1, inv, half, mode);
   const float fl = floorf(idx);
   Tap t;

@@ -28,8 +28,10 @@ namespace {
 
 using namespace lk;
 
-constexpr int kWarpsTma = 16;                         // one query per warp per pipeline unit
-constexpr int kThreadsTma = kWarpsTma * 32;
+constexpr int kWarpsTma = 16;                         // sampling warps: one query per warp per unit
+constexpr int kStagers = 8;                           // staging warps: each feeds two sampling warps
+constexpr int kSamplerThreads = kWarpsTma * 32;
+constexpr int kThreadsTma = (kWarpsTma + kStagers) * 32;
 constexpr int kUnitQ = 16;                            // queries per unit (half an output tile)
 constexpr int kDepth = 3;                             // units buffered per warp (2 in flight)
 constexpr int kBoxW = 16;                             // staged window: 16 columns ...
@@ -71,7 +73,7 @@ struct Cfg {
   static constexpr int kOffWin = kOffTab + kTabBytes;            // [warp][depth][L] int4
   static constexpr int kWinBytes = kWarpsTma * kDepth * RAFTCORR_MAX_LEVELS * 16;
   static constexpr int kOffBars = kOffWin + kWinBytes;
-  static constexpr int kSmem = kOffBars + kWarpsTma * kDepth * 8;
+  static constexpr int kSmem = kOffBars + 2 * kWarpsTma * kDepth * 8;   // full[w][s], empty[w][s]
 };
 
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
@@ -95,12 +97,16 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
   const uint32_t smem_base = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* out_s = reinterpret_cast<float*>(smem + C::kOffOut);
-  Tap* tab_w = reinterpret_cast<Tap*>(smem + C::kOffTab) + warp * (kDepth * kTabEntries);
-  int4* win_w = reinterpret_cast<int4*>(smem + C::kOffWin) + warp * (kDepth * RAFTCORR_MAX_LEVELS);
-  const uint32_t bar0 = smem_base + C::kOffBars + warp * kDepth * 8;   // this warp's mbarriers
+  auto tab_of = [&](int w) { return reinterpret_cast<Tap*>(smem + C::kOffTab) + w * (kDepth * kTabEntries); };
+  auto win_of = [&](int w) { return reinterpret_cast<int4*>(smem + C::kOffWin) + w * (kDepth * RAFTCORR_MAX_LEVELS); };
+  auto full_bar = [&](int w, int s) { return smem_base + C::kOffBars + (w * kDepth + s) * 8; };
+  auto empty_bar = [&](int w, int s) { return smem_base + C::kOffBars + ((kWarpsTma + w) * kDepth + s) * 8; };
 
-  if (lane == 0) {
-    for (int s = 0; s < kDepth; ++s) mbar_init(bar0 + 8 * s, 1);
+  if (threadIdx.x < kWarpsTma) {
+    for (int s = 0; s < kDepth; ++s) {
+      mbar_init(full_bar(threadIdx.x, s), 1);    // stager's arrive.expect_tx (+ TMA bytes)
+      mbar_init(empty_bar(threadIdx.x, s), 1);   // sampler's lane 0
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -123,155 +129,172 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
     c.y = (int)(t2 - (unsigned)c.b * (unsigned)p.H);
     return c;
   };
-  // lanes 0/1 fetch x/y of this warp's query in (tile cursor, half); 0 when it does not exist
-  auto load_coord = [&](const Cursor& c, int half) -> float {
-    float v = 0.0f;
-    const int x = c.x0 + half * kUnitQ + warp;
-    if (c.live && lane < 2 && x < p.W)
-      v = __ldg(p.coords + ((long long)c.b * 2 + lane) * N + (long long)c.y * p.W + x);
-    return v;
-  };
 
-  // per-lane description of the tap this lane evaluates in each round of the tap-table phase
-  float t_sm1[C::kTapRounds], t_inv[C::kTapRounds], t_half[C::kTapRounds], t_pow[C::kTapRounds];
-  int t_off[C::kTapRounds], t_slot[C::kTapRounds];
-  bool t_isy[C::kTapRounds];
+  if (warp >= kWarpsTma) {
+    // ================================ staging warps ================================
+    // Warp g feeds sampling warps 2g and 2g+1: tap table -> window geometry -> one TMA box per
+    // level, into ring slot (unit % kDepth) of that sampling warp.
+    const int g = warp - kWarpsTma;
+    float t_sm1[C::kTapRounds], t_inv[C::kTapRounds], t_half[C::kTapRounds], t_pow[C::kTapRounds], t_off[C::kTapRounds];
+    int t_slot[C::kTapRounds];
+    bool t_isy[C::kTapRounds];
 #pragma unroll
-  for (int r = 0; r < C::kTapRounds; ++r) {
-    const int t = r * 32 + lane;
-    const int tt = t < C::kTaps ? t : 0;
-    const int l = tt / (2 * rd);
-    const int rem = tt - l * 2 * rd;
-    const int axis = rem >= rd;
-    const int tap = rem - axis * rd;
-    const LevelDev& lv = p.lv[l];
-    t_sm1[r] = axis ? lv.sm1y : lv.sm1x;
-    t_inv[r] = axis ? lv.invy : lv.invx;
-    t_half[r] = axis ? lv.halfy : lv.halfx;
-    t_pow[r] = lv.inv_pow2;
-    t_off[r] = tap - R;
-    t_isy[r] = axis;
-    t_slot[r] = t < C::kTaps ? (l * 2 + axis) * kMaxRd + tap : -1;
-  }
-
-  // Stage one unit: tap table -> window geometry -> one TMA box per level into ring slot s.
-  auto stage = [&](const Cursor& c, int half, int s, float cmine) {
-    const int x = c.x0 + half * kUnitQ + warp;
-    if (!c.live || x >= p.W) return;
-    const float cx = __shfl_sync(0xffffffffu, cmine, 0), cy = __shfl_sync(0xffffffffu, cmine, 1);
-    Tap* tab = tab_w + s * kTabEntries;
-#pragma unroll
-    for (int r = 0; r < C::kTapRounds; ++r)
-      if (t_slot[r] >= 0)
-        tab[t_slot[r]] = make_tap_fast(__fmul_rn(t_isy[r] ? cy : cx, t_pow[r]), t_off[r], t_sm1[r], t_inv[r],
-                                  t_half[r], kMode);
-    __syncwarp();
-    if (lane < L) {
-      const Tap* tx = tab + (lane * 2 + 0) * kMaxRd;
-      const Tap* ty = tab + (lane * 2 + 1) * kMaxRd;
-      const int x_lo = tx[0].i0, y_lo = ty[0].i0;
-      const int wdt = tx[rd - 1].i0 + 2 - x_lo, hgt = ty[rd - 1].i0 + 2 - y_lo;
-      const int fast = (wdt >= 1) & (wdt <= kFoot) & (hgt >= 1) & (hgt <= kFoot);
-      const int h = hgt < 10 ? 10 : (hgt > 12 ? 12 : hgt);
-      // .x: box column of a tap with floor index i0 is (i0 + .x); .y: first row; .z: box height; .w: fast
-      win_w[s * RAFTCORR_MAX_LEVELS + lane] = make_int4((x_lo & 3) - x_lo, y_lo, h, fast);
+    for (int r = 0; r < C::kTapRounds; ++r) {
+      const int t = r * 32 + lane;
+      const int tt = t < C::kTaps ? t : 0;
+      const int l = tt / (2 * rd);
+      const int rem = tt - l * 2 * rd;
+      const int axis = rem >= rd;
+      const int tap = rem - axis * rd;
+      const LevelDev& lv = p.lv[l];
+      t_sm1[r] = axis ? lv.sm1y : lv.sm1x;
+      t_inv[r] = axis ? lv.invy : lv.invx;
+      t_half[r] = axis ? lv.halfy : lv.halfx;
+      t_pow[r] = lv.inv_pow2;
+      t_off[r] = (float)(tap - R);
+      t_isy[r] = axis;
+      t_slot[r] = t < C::kTaps ? (l * 2 + axis) * kMaxRd + tap : -1;
     }
-    __syncwarp();
-    if (elect_one()) {
-      const uint32_t bar = bar0 + 8 * s;
-      const int q = (int)((long long)c.b * N + (long long)c.y * p.W + x);
-      const uint32_t dst = smem_base + (s * kWarpsTma + warp) * kWarpBufBytes;
-      int4 w[L];
-      uint32_t bytes = 0;
+    // lanes 0..3 fetch (x, y) of the two queries this warp stages in a unit
+    auto load_coords = [&](const Cursor& c, int half) -> float {
+      float v = 0.0f;
+      const int x = c.x0 + half * kUnitQ + 2 * g + (lane >> 1);
+      if (c.live && lane < 4 && x < p.W)
+        v = __ldg(p.coords + ((long long)c.b * 2 + (lane & 1)) * N + (long long)c.y * p.W + x);
+      return v;
+    };
+    uint32_t ephase = 0x3fu;  // bit (cc*kDepth+s): parity to wait for on empty[2g+cc][s]; fresh = passes
+    int slot = 0;
+    Cursor cur = cursor_at(0), nxt = cursor_at(1);
+    float cnow = load_coords(cur, 0);
+    for (int k = 0; k < n_tiles; ++k) {
 #pragma unroll
-      for (int l = 0; l < L; ++l) {
-        w[l] = win_w[s * RAFTCORR_MAX_LEVELS + l];
-        bytes += (uint32_t)(w[l].z * kBoxW * 4);
-      }
-      mbar_expect_tx(bar, bytes);
+      for (int half = 0; half < 2; ++half) {
+        const float cnext = half == 0 ? load_coords(cur, 1) : load_coords(nxt, 0);   // one unit ahead
 #pragma unroll
-      for (int l = 0; l < L; ++l) {
-        // box start = x_lo & ~3 = -(w.x); windows entirely outside the image are all zeros
-        // wherever the box sits, so far-away origins are clamped to keep the coordinates sane
-        const int bx = max(-64, min(-w[l].x, (p.lv[l].W + 64) & ~3));
-        const int by = max(-64, min(w[l].y, p.lv[l].H + 64));
-        const CUtensorMap* m = w[l].z == 10 ? &maps.m[l][0] : (w[l].z == 11 ? &maps.m[l][1] : &maps.m[l][2]);
-        tma_load_3d(dst + l * kSlotBytes, m, bar, bx, by, q);
+        for (int cc = 0; cc < 2; ++cc) {
+          const int w = 2 * g + cc;
+          const int x = cur.x0 + half * kUnitQ + w;
+          if (x < p.W) {
+            const float cx = __shfl_sync(0xffffffffu, cnow, 2 * cc), cy = __shfl_sync(0xffffffffu, cnow, 2 * cc + 1);
+            const int bit = cc * kDepth + slot;
+            mbar_wait(empty_bar(w, slot), (ephase >> bit) & 1u, 1);
+            ephase ^= 1u << bit;
+            Tap* tab = tab_of(w) + slot * kTabEntries;
+            int4* win = win_of(w) + slot * RAFTCORR_MAX_LEVELS;
+#pragma unroll
+            for (int r = 0; r < C::kTapRounds; ++r)
+              if (t_slot[r] >= 0)
+                tab[t_slot[r]] = make_tap_fast(__fmul_rn(t_isy[r] ? cy : cx, t_pow[r]), t_off[r], t_sm1[r],
+                                               t_inv[r], t_half[r], kMode);
+            __syncwarp();
+            if (lane < L) {
+              const Tap* tx = tab + (lane * 2 + 0) * kMaxRd;
+              const Tap* ty = tab + (lane * 2 + 1) * kMaxRd;
+              const int x_lo = tx[0].i0, y_lo = ty[0].i0;
+              const int wdt = tx[rd - 1].i0 + 2 - x_lo, hgt = ty[rd - 1].i0 + 2 - y_lo;
+              const int fast = (wdt >= 1) & (wdt <= kFoot) & (hgt >= 1) & (hgt <= kFoot);
+              const int h = hgt < 10 ? 10 : (hgt > 12 ? 12 : hgt);
+              // .x: box column of a tap with floor index i0 is (i0 + .x); .y: first row; .z: box height; .w: fast
+              win[lane] = make_int4((x_lo & 3) - x_lo, y_lo, h, fast);
+            }
+            __syncwarp();
+            if (elect_one()) {
+              const uint32_t bar = full_bar(w, slot);
+              const int q = (int)((long long)cur.b * N + (long long)cur.y * p.W + x);
+              const uint32_t dst = smem_base + (slot * kWarpsTma + w) * kWarpBufBytes;
+              int4 wv[L];
+              uint32_t bytes = 0;
+#pragma unroll
+              for (int l = 0; l < L; ++l) {
+                wv[l] = win[l];
+                bytes += (uint32_t)(wv[l].z * kBoxW * 4);
+              }
+              mbar_expect_tx(bar, bytes);   // release: the tap table and windows above are visible to the waiter
+#pragma unroll
+              for (int l = 0; l < L; ++l) {
+                // box start = x_lo & ~3 = -(w.x); windows entirely outside the image are all zeros
+                // wherever the box sits, so far-away origins are clamped to keep the coordinates sane
+                const int bx = max(-64, min(-wv[l].x, (p.lv[l].W + 64) & ~3));
+                const int by = max(-64, min(wv[l].y, p.lv[l].H + 64));
+                const CUtensorMap* m = wv[l].z == 10 ? &maps.m[l][0] : (wv[l].z == 11 ? &maps.m[l][1] : &maps.m[l][2]);
+                tma_load_3d(dst + l * kSlotBytes, m, bar, bx, by, q);
+              }
+            }
+            __syncwarp();
+          }
+        }
+        cnow = cnext;
+        slot = slot + 1 == kDepth ? 0 : slot + 1;
       }
+      cur = nxt;
+      nxt = cursor_at(k + 2);
     }
-  };
-
-  // sampling phase: lane = i * 3 + jb handles x tap i and y taps j = 3 * jb + jj
-  const int ti = lane / C::kJGroups;
-  const int tj0 = (lane - ti * C::kJGroups) * C::kJPer;
-
-  Cursor cur = cursor_at(0), nxt = cursor_at(1), nxt2 = cursor_at(2);
-  stage(cur, 0, 0, load_coord(cur, 0));   // prologue: two units in flight
-  stage(cur, 1, 1, load_coord(cur, 1));
-  float cnext = load_coord(nxt, 0);       // coordinates are fetched one unit ahead of staging
-  uint32_t phases = 0;                    // bit s = parity of the next completion of ring slot s
-  int slot = 0;                           // ring slot of the unit being sampled
-
-  for (int k = 0; k < n_tiles; ++k) {
+  } else {
+    // ================================ sampling warps ================================
+    // lane = i * 3 + jb handles x tap i and y taps j = 3 * jb + jj of this warp's query
+    const int ti = lane / C::kJGroups;
+    const int tj0 = (lane - ti * C::kJGroups) * C::kJPer;
+    const Tap* tab_w = tab_of(warp);
+    const int4* win_w = win_of(warp);
+    uint32_t phases = 0;   // bit s = parity of the next completion of full[warp][s]
+    int slot = 0;
+    Cursor cur = cursor_at(0);
+    for (int k = 0; k < n_tiles; ++k) {
+      const Cursor nxt = cursor_at(k + 1);
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      {
-        int s2 = slot + 2;
-        s2 = s2 >= kDepth ? s2 - kDepth : s2;
-        stage(nxt, half, s2, cnext);      // unit two ahead: same half of the next tile
-        cnext = half == 0 ? load_coord(nxt, 1) : load_coord(nxt2, 0);
-      }
-      const int x = cur.x0 + half * kUnitQ + warp;
-      const int qi = half * kUnitQ + warp;
-      if (x < p.W) {
-        mbar_wait(bar0 + 8 * slot, (phases >> slot) & 1u, 2);
-        phases ^= 1u << slot;
-        if (lane < C::kActive) {
-          const Tap* tab = tab_w + slot * kTabEntries;
-          const float* buf = reinterpret_cast<const float*>(smem + (slot * kWarpsTma + warp) * kWarpBufBytes);
+      for (int half = 0; half < 2; ++half) {
+        const int x = cur.x0 + half * kUnitQ + warp;
+        const int qi = half * kUnitQ + warp;
+        if (x < p.W) {
+          mbar_wait(full_bar(warp, slot), (phases >> slot) & 1u, 2);
+          phases ^= 1u << slot;
+          if (lane < C::kActive) {
+            const Tap* tab = tab_w + slot * kTabEntries;
+            const float* buf = reinterpret_cast<const float*>(smem + (slot * kWarpsTma + warp) * kWarpBufBytes);
 #pragma unroll
-          for (int l = 0; l < L; ++l) {
-            const int4 w = win_w[slot * RAFTCORR_MAX_LEVELS + l];
-            const Tap a = tab[(l * 2 + 0) * kMaxRd + ti];
-            const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
-            const float* f = buf + l * (kSlotBytes / 4) + (a.i0 + w.x);
-            float* o = out_s + (l * rd2 + ti * rd) * kOutPitch + qi;
+            for (int l = 0; l < L; ++l) {
+              const int4 w = win_w[slot * RAFTCORR_MAX_LEVELS + l];
+              const Tap a = tab[(l * 2 + 0) * kMaxRd + ti];
+              const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
+              const float* f = buf + l * (kSlotBytes / 4) + (a.i0 + w.x);
+              float* o = out_s + (l * rd2 + ti * rd) * kOutPitch + qi;
 #pragma unroll
-            for (int jj = 0; jj < C::kJPer; ++jj) {
-              const int j = tj0 + jj;
-              if (j < rd) {
-                const Tap c = ty[j];
-                float v;
-                if (w.w) {
-                  const float* g = f + (c.i0 - w.y) * kBoxW;
-                  v = bilinear_combine(g[0], g[1], g[kBoxW], g[kBoxW + 1], a.frac, c.frac);
-                } else {
-                  v = sample_direct(p.lv[l], (long long)cur.b * N + (long long)cur.y * p.W + x, a, c);
+              for (int jj = 0; jj < C::kJPer; ++jj) {
+                const int j = tj0 + jj;
+                if (j < rd) {
+                  const Tap c = ty[j];
+                  float v;
+                  if (w.w) {
+                    const float* gp = f + (c.i0 - w.y) * kBoxW;
+                    v = bilinear_combine(gp[0], gp[1], gp[kBoxW], gp[kBoxW + 1], a.frac, c.frac);
+                  } else {
+                    v = sample_direct(p.lv[l], (long long)cur.b * N + (long long)cur.y * p.W + x, a, c);
+                  }
+                  o[j * kOutPitch] = v;
                 }
-                o[j * kOutPitch] = v;
               }
             }
           }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(empty_bar(warp, slot));   // ring slot may be refilled
+        }
+        slot = slot + 1 == kDepth ? 0 : slot + 1;
+      }
+      // both halves of the output tile are in shared memory: write it out as 128-byte rows
+      named_bar_sync(1, kSamplerThreads);
+      {
+        const int xx = cur.x0 + lane;
+        if (xx < p.W) {
+          float* dst = p.out + (long long)cur.b * C::kChannels * N + (long long)cur.y * p.W + xx;
+#pragma unroll 4
+          for (int c = warp; c < C::kChannels; c += kWarpsTma)
+            __stcs(dst + (long long)c * N, out_s[c * kOutPitch + lane]);
         }
       }
-      __syncwarp();
-      slot = slot + 1 == kDepth ? 0 : slot + 1;
+      named_bar_sync(1, kSamplerThreads);
+      cur = nxt;
     }
-    // both halves of the output tile are in shared memory: write it out as 128-byte rows
-    named_bar_sync(1, kThreadsTma);
-    {
-      const int xx = cur.x0 + lane;
-      if (xx < p.W) {
-        float* dst = p.out + (long long)cur.b * C::kChannels * N + (long long)cur.y * p.W + xx;
-#pragma unroll 4
-        for (int c = warp; c < C::kChannels; c += kWarpsTma)
-          __stcs(dst + (long long)c * N, out_s[c * kOutPitch + lane]);
-      }
-    }
-    named_bar_sync(1, kThreadsTma);
-    cur = nxt;
-    nxt = nxt2;
-    nxt2 = cursor_at(k + 3);
   }
 }
 
