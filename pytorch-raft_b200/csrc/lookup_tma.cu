@@ -88,6 +88,30 @@ __device__ __noinline__ float sample_direct(const LevelDev& lv, long long q, Tap
                           a.frac, c.frac);
 }
 
+// A query with at least one window that does not fit the staged box (|coords| beyond ~2^20, where
+// fp32 spacing breaks the tap pattern): per-sample choice between the staged box and global memory.
+template <int R, int L>
+__device__ __noinline__ void sample_query_slow(const LookupTmaParams& p, const Tap* tab, const int4* wv,
+                                               const float* buf, float* out_s, long long q, int qi, int lane) {
+  constexpr int rd = 2 * R + 1, rd2 = rd * rd;
+  for (int l = 0; l < L; ++l) {
+    const Tap* tx = tab + (l * 2 + 0) * kMaxRd;
+    const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
+    for (int k = lane; k < rd2; k += 32) {
+      const int i = k / rd, j = k - i * rd;
+      const Tap a = tx[i], c = ty[j];
+      float v;
+      if (wv[l].w) {
+        const float* gp = buf + l * (kSlotBytes / 4) + (c.i0 - wv[l].y) * kBoxW + (a.i0 + wv[l].x);
+        v = bilinear_combine(gp[0], gp[1], gp[kBoxW], gp[kBoxW + 1], a.frac, c.frac);
+      } else {
+        v = sample_direct(p.lv[l], q, a, c);
+      }
+      out_s[(l * rd2 + k) * kOutPitch + qi] = v;
+    }
+  }
+}
+
 template <int R, int L, int kMode>
 __global__ void __launch_bounds__(kThreadsTma, 1)
 lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_constant__ LookupTmaMaps maps) {
@@ -178,7 +202,7 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
           if (x < p.W) {
             const float cx = __shfl_sync(0xffffffffu, cnow, 2 * cc), cy = __shfl_sync(0xffffffffu, cnow, 2 * cc + 1);
             const int bit = cc * kDepth + slot;
-            mbar_wait(empty_bar(w, slot), (ephase >> bit) & 1u, 1);
+            mbar_wait_relaxed(empty_bar(w, slot), (ephase >> bit) & 1u, 1);
             ephase ^= 1u << bit;
             Tap* tab = tab_of(w) + slot * kTabEntries;
             int4* win = win_of(w) + slot * RAFTCORR_MAX_LEVELS;
@@ -217,7 +241,7 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
                 // wherever the box sits, so far-away origins are clamped to keep the coordinates sane
                 const int bx = max(-64, min(-wv[l].x, (p.lv[l].W + 64) & ~3));
                 const int by = max(-64, min(wv[l].y, p.lv[l].H + 64));
-                const CUtensorMap* m = wv[l].z == 10 ? &maps.m[l][0] : (wv[l].z == 11 ? &maps.m[l][1] : &maps.m[l][2]);
+                const CUtensorMap* m = &maps.m[l][0] + (wv[l].z - 10);
                 tma_load_3d(dst + l * kSlotBytes, m, bar, bx, by, q);
               }
             }
@@ -249,32 +273,36 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
         if (x < p.W) {
           mbar_wait(full_bar(warp, slot), (phases >> slot) & 1u, 2);
           phases ^= 1u << slot;
-          if (lane < C::kActive) {
-            const Tap* tab = tab_w + slot * kTabEntries;
-            const float* buf = reinterpret_cast<const float*>(smem + (slot * kWarpsTma + warp) * kWarpBufBytes);
+          const Tap* tab = tab_w + slot * kTabEntries;
+          const float* buf = reinterpret_cast<const float*>(smem + (slot * kWarpsTma + warp) * kWarpBufBytes);
+          int4 wv[L];
+          int all_fast = 1;
 #pragma unroll
-            for (int l = 0; l < L; ++l) {
-              const int4 w = win_w[slot * RAFTCORR_MAX_LEVELS + l];
-              const Tap a = tab[(l * 2 + 0) * kMaxRd + ti];
-              const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
-              const float* f = buf + l * (kSlotBytes / 4) + (a.i0 + w.x);
-              float* o = out_s + (l * rd2 + ti * rd) * kOutPitch + qi;
+          for (int l = 0; l < L; ++l) {
+            wv[l] = win_w[slot * RAFTCORR_MAX_LEVELS + l];
+            all_fast &= wv[l].w;
+          }
+          if (all_fast) {
+            // common case, branch-free so the 12 samples of a lane overlap their shared-memory latency
+            if (lane < C::kActive) {
 #pragma unroll
-              for (int jj = 0; jj < C::kJPer; ++jj) {
-                const int j = tj0 + jj;
-                if (j < rd) {
+              for (int l = 0; l < L; ++l) {
+                const Tap a = tab[(l * 2 + 0) * kMaxRd + ti];
+                const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
+                const float* f = buf + l * (kSlotBytes / 4) + (a.i0 + wv[l].x) - wv[l].y * kBoxW;
+                float* o = out_s + (l * rd2 + ti * rd) * kOutPitch + qi;
+#pragma unroll
+                for (int jj = 0; jj < C::kJPer; ++jj) {
+                  const int j = (tj0 + jj < rd) ? tj0 + jj : rd - 1;   // clamp keeps the loads in range
                   const Tap c = ty[j];
-                  float v;
-                  if (w.w) {
-                    const float* gp = f + (c.i0 - w.y) * kBoxW;
-                    v = bilinear_combine(gp[0], gp[1], gp[kBoxW], gp[kBoxW + 1], a.frac, c.frac);
-                  } else {
-                    v = sample_direct(p.lv[l], (long long)cur.b * N + (long long)cur.y * p.W + x, a, c);
-                  }
-                  o[j * kOutPitch] = v;
+                  const float* gp = f + c.i0 * kBoxW;
+                  const float v = bilinear_combine(gp[0], gp[1], gp[kBoxW], gp[kBoxW + 1], a.frac, c.frac);
+                  if (tj0 + jj < rd) o[j * kOutPitch] = v;
                 }
               }
             }
+          } else {
+            sample_query_slow<R, L>(p, tab, win_w + slot * RAFTCORR_MAX_LEVELS, buf, out_s, (long long)cur.b * N + (long long)cur.y * p.W + x, qi, lane);
           }
           __syncwarp();
           if (lane == 0) mbar_arrive(empty_bar(warp, slot));   // ring slot may be refilled

@@ -37,31 +37,55 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 #ifdef RAFTCORR_DEBUG_TIMEOUT
 __device__ unsigned long long g_wait_timeout[8];
 #endif
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(done)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return done != 0;
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int tag = 0) {
+  if (mbar_try(bar, parity)) return;
   const long long t0 = clock64();
-  uint32_t done = 0;
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.b32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (done) return;
+  for (uint32_t spins = 1;; ++spins) {
+    if (mbar_try(bar, parity)) return;
+    if ((spins & 63u) == 0) {   // the clock is only consulted now and then: keep the spin cheap
 #ifdef RAFTCORR_DEBUG_TIMEOUT
-    if (clock64() - t0 > 100000000LL) {
-      if ((threadIdx.x & 31) == 0) {
-        atomicAdd(&g_wait_timeout[0], 1ULL);
-        atomicMax(&g_wait_timeout[1 + (tag & 3)],
-                  ((unsigned long long)(blockIdx.x + 1) << 32) | ((unsigned long long)(threadIdx.x >> 5) << 8) | parity);
+      if (clock64() - t0 > 100000000LL) {
+        if ((threadIdx.x & 31) == 0) {
+          atomicAdd(&g_wait_timeout[0], 1ULL);
+          atomicMax(&g_wait_timeout[1 + (tag & 3)],
+                    ((unsigned long long)(blockIdx.x + 1) << 32) | ((unsigned long long)(threadIdx.x >> 5) << 8) | parity);
+        }
+        return;
       }
-      return;
-    }
 #else
-    (void)tag;
-    if (clock64() - t0 > 8000000000LL) __trap();
+      (void)tag;
+      if (clock64() - t0 > 8000000000LL) __trap();
 #endif
+    }
+  }
+}
+// same, for a warp that is merely running ahead (producer waiting for a free slot): back off so
+// the spin does not steal issue slots from the warps doing the work
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity, int tag = 0) {
+  if (mbar_try(bar, parity)) return;
+  const long long t0 = clock64();
+  for (uint32_t spins = 1;; ++spins) {
+    __nanosleep(256);
+    if (mbar_try(bar, parity)) return;
+    if ((spins & 63u) == 0) {
+#ifdef RAFTCORR_DEBUG_TIMEOUT
+      if (clock64() - t0 > 100000000LL) return;
+#else
+      (void)tag;
+      if (clock64() - t0 > 8000000000LL) __trap();
+#endif
+    }
   }
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0,
