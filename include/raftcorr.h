@@ -125,6 +125,16 @@ int raftcorr_build_bwd(const raftcorr_level* grad_levels, int num_levels, const 
 int raftcorr_alt_fwd(const float* fmap1, const float* fmap2, const float* coords, float* corr,
                      int B, int H1, int W1, int H2, int W2, int C, int radius, int coord_mode,
                      float scale, void* stream);
+/* The same path fused over all levels on the tensor cores: replaces one whole
+ * AlternateCorrBlock.__call__ (core/corr.py:74-91: num_levels launches + NHWC copies + stack + divide).
+ *      fmap1_bf16: (B,H1,W1,C) NHWC bfloat16; fmap2_bf16[l]: (B,H1>>l,W1>>l,C) NHWC bfloat16, the 2x2
+ *      mean-pooled fmap2 pyramid of core/corr.py:68-72; coords: (B,2,H1,W1) fp32 in level-0 pixels
+ *      (the kernel applies the /2^l of corr.py:85); out: (B, L*(2r+1)^2, H1, W1) fp32, multiplied by
+ *      `scale` (1/sqrt(C) reproduces corr.py:91).  bf16 products, fp32 accumulation: <=1e-2 of max|ref|. */
+int raftcorr_alt_fused_fwd(const void* fmap1_bf16, const void* const* fmap2_bf16, const float* coords,
+                           float* out, int B, int H1, int W1, int C, int num_levels, int radius,
+                           int coord_mode, float scale, void* stream);
+
 /* fmap1_grad/fmap2_grad must be zero-filled by the caller (accumulated with atomics);
  * coords_grad may be NULL.  The reference returns coords_grad as all zeros
  * (correlation_kernel.cu:130,307,323); this library fills it (documented superset). */

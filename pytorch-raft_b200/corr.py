@@ -65,15 +65,25 @@ class AlternateCorrBlock:
 
     ``pyramid`` keeps the reference's list of pooled (fmap1, fmap2) pairs (num_levels+1 entries,
     corr.py:68-72).  The NHWC copies the reference re-creates on every call (corr.py:82-83) are
-    made once here.  Each level is one launch of the on-the-fly kernel; the 1/sqrt(D) of
-    corr.py:91 is folded into it.  ``coord_mode`` defaults to CorrBlock's coordinate semantics
-    so both blocks produce identical zero-padding masks; pass 'direct' for the reference CUDA
-    kernel's floor(coords) behaviour (correlation_kernel.cu:66-76)."""
+    made once here.
 
-    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, *, coord_mode=None):
+    ``precision='bf16'`` (default without autograd): one fused tensor-core launch per call — the
+    windows of a tile of 128 neighbouring queries overlap, so their union is a small dense GEMM
+    against bf16 NHWC copies of fmap1 and the pooled fmap2 pyramid (csrc/alt_tc.cu); the 1/sqrt(D) of
+    corr.py:91 and the /2^l of corr.py:85 are folded in.  ``precision='fp32'`` (and any call that
+    needs gradients): one fp32 CUDA-core launch per level (csrc/alt.cu), differentiable.
+
+    ``coord_mode`` defaults to CorrBlock's coordinate semantics so both blocks produce identical
+    zero-padding masks; pass 'direct' for the reference CUDA kernel's floor(coords) behaviour
+    (correlation_kernel.cu:66-76)."""
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, *, coord_mode=None, precision=None):
         self.num_levels = num_levels
         self.radius = radius
         self._coord_mode = ops.resolve_coord_mode(coord_mode)
+        if precision not in (None, "bf16", "fp32"):
+            raise ValueError("AlternateCorrBlock precision must be 'bf16' or 'fp32'")
+        self._precision = precision or "bf16"
         self.pyramid = [(fmap1, fmap2)]
         for _ in range(self.num_levels):
             fmap1 = F.avg_pool2d(fmap1, 2, stride=2)
@@ -81,14 +91,21 @@ class AlternateCorrBlock:
             self.pyramid.append((fmap1, fmap2))
         self._f1 = self.pyramid[0][0].permute(0, 2, 3, 1).contiguous()
         self._f2 = [self.pyramid[i][1].permute(0, 2, 3, 1).contiguous() for i in range(num_levels)]
+        self._f1_bf16 = self._f2_bf16 = None
+        dim = self._f1.shape[-1]
+        if self._precision == "bf16" and dim % 8 == 0 and dim <= 256 and radius in (3, 4):
+            self._f1_bf16 = self._f1.detach().to(torch.bfloat16)
+            self._f2_bf16 = [t.detach().to(torch.bfloat16) for t in self._f2]
 
     def __call__(self, coords):
-        coords = coords.permute(0, 2, 3, 1)
-        B, H, W, _ = coords.shape
         dim = self._f1.shape[-1]
         scale = 1.0 / math.sqrt(dim)
         graph = torch.is_grad_enabled() and (coords.requires_grad or self._f1.requires_grad
                                              or self._f2[0].requires_grad)
+        if self._f1_bf16 is not None and not graph:
+            return ops.alt_fused_forward(self._f1_bf16, self._f2_bf16, coords, self.radius, self._coord_mode, scale)
+        coords = coords.permute(0, 2, 3, 1)
+        B, H, W, _ = coords.shape
         corr_list = []
         for i in range(self.num_levels):
             coords_i = (coords / 2 ** i).reshape(B, 1, H, W, 2).contiguous()

@@ -48,6 +48,8 @@ int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, cons
                      cudaStream_t stream);
 int launch_alt_fwd(const float* f1, const float* f2, const float* coords, float* corr, int B, int H1,
                    int W1, int H2, int W2, int C, int r, int mode, float scale, cudaStream_t stream);
+int launch_alt_tc(const void* f1_bf16, const void* const* f2_bf16, const float* coords, float* out, int B,
+                  int H1, int W1, int C, int L, int r, int mode, float scale, cudaStream_t stream);
 int launch_alt_bwd(const float* f1, const float* f2, const float* coords, const float* gcorr,
                    float* g1, float* g2, float* gcoords, int B, int H1, int W1, int H2, int W2, int C,
                    int r, int mode, float scale, cudaStream_t stream);
@@ -186,6 +188,19 @@ int raftcorr_alt_fwd(const float* fmap1, const float* fmap2, const float* coords
   RC_REQUIRE(valid_mode(coord_mode), "alt_fwd: coord_mode=%d", coord_mode);
   return launch_alt_fwd(fmap1, fmap2, coords, corr, B, H1, W1, H2, W2, C, radius, coord_mode, scale,
                         (cudaStream_t)stream);
+}
+
+int raftcorr_alt_fused_fwd(const void* fmap1_bf16, const void* const* fmap2_bf16, const float* coords,
+                           float* out, int B, int H1, int W1, int C, int num_levels, int radius,
+                           int coord_mode, float scale, void* stream) {
+  RC_REQUIRE(fmap1_bf16 && fmap2_bf16 && coords && out, "alt_fused_fwd: NULL pointer");
+  RC_REQUIRE(B >= 0 && H1 >= 1 && W1 >= 1 && C >= 1, "alt_fused_fwd: bad sizes");
+  RC_REQUIRE(num_levels >= 1 && num_levels <= RAFTCORR_MAX_LEVELS, "alt_fused_fwd: num_levels=%d", num_levels);
+  RC_REQUIRE(valid_mode(coord_mode), "alt_fused_fwd: coord_mode=%d", coord_mode);
+  for (int l = 0; l < num_levels; ++l) RC_REQUIRE(fmap2_bf16[l] != nullptr, "alt_fused_fwd: fmap2 level %d is NULL", l);
+  RC_REQUIRE(!(reinterpret_cast<uintptr_t>(fmap1_bf16) & 15), "alt_fused_fwd: fmap1 must be 16-byte aligned");
+  return launch_alt_tc(fmap1_bf16, fmap2_bf16, coords, out, B, H1, W1, C, num_levels, radius, coord_mode, scale,
+                       (cudaStream_t)stream);
 }
 
 int raftcorr_alt_bwd(const float* fmap1, const float* fmap2, const float* coords,

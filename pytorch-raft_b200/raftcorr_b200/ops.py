@@ -176,6 +176,24 @@ def alt_forward(fmap1: torch.Tensor, fmap2: torch.Tensor, coords: torch.Tensor, 
     return corr
 
 
+def alt_fused_forward(fmap1_bf16: torch.Tensor, fmap2_bf16: Sequence[torch.Tensor], coords: torch.Tensor,
+                      radius: int, coord_mode=None, scale: float = 1.0) -> torch.Tensor:
+    """All levels of the on-the-fly path in one tensor-core launch (replaces corr.py:74-91).
+    fmap1_bf16 (B,H,W,C) and fmap2_bf16[l] (B,H>>l,W>>l,C) are NHWC bfloat16; coords (B,2,H,W) fp32."""
+    B, H, W, C = fmap1_bf16.shape
+    L = len(fmap2_bf16)
+    coords = coords.contiguous()
+    _require_cuda_f32(coords, "coords")
+    rd = 2 * radius + 1
+    out = torch.empty((B, L * rd * rd, H, W), dtype=torch.float32, device=coords.device)
+    ptrs = (ctypes.c_void_p * L)(*[t.data_ptr() for t in fmap2_bf16])
+    with _on_device(coords.device):
+        _capi.check(_capi.lib().raftcorr_alt_fused_fwd(fmap1_bf16.data_ptr(), ptrs, coords.data_ptr(), out.data_ptr(),
+                                                       B, H, W, C, L, radius, resolve_coord_mode(coord_mode), scale,
+                                                       _stream(coords)), "raftcorr_alt_fused_fwd")
+    return out
+
+
 def alt_backward(fmap1, fmap2, coords, corr_grad, radius: int, coord_mode=COORD_DIRECT,
                  scale: float = 1.0, want_coords: bool = True):
     B, H1, W1, C = fmap1.shape

@@ -81,21 +81,67 @@ def test_no_grad_builds_no_graph(golden):
     assert not out.requires_grad and out.grad_fn is None
 
 
-@pytest.mark.parametrize("kind", ("grid", "sigma4", "sigma30"))
-def test_alternate_corr_block_matches_corrblock_golden(golden, kind):
+@pytest.mark.parametrize("kind", ("grid", "half", "sigma4", "sigma30"))
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-5), ("bf16", 1e-2)])
+def test_alternate_corr_block_matches_corrblock_golden(golden, kind, precision, tol):
     """AlternateCorrBlock computes the same numbers as CorrBlock (pooling commutes with the dot
-    product); with CorrBlock's coordinate semantics the zero masks agree exactly as well."""
+    product); with CorrBlock's coordinate semantics the zero masks agree exactly as well.
+    'bf16' is the fused tensor-core kernel (csrc/alt_tc.cu), 'fp32' the per-level CUDA-core one."""
     import corr
     g = golden("corr_tiny")
     with torch.no_grad():
-        blk = corr.AlternateCorrBlock(_t(g["fmap1"]), _t(g["fmap2"]), num_levels=4, radius=4)
+        blk = corr.AlternateCorrBlock(_t(g["fmap1"]), _t(g["fmap2"]), num_levels=4, radius=4, precision=precision)
         out = blk(_t(g[f"coords_{kind}"]))
     assert len(blk.pyramid) == 5 and blk.pyramid[1][1].shape == (1, 8, 8, 9)
     ref = g[f"out_{kind}"]
     o = out.cpu().numpy()
-    assert o.shape == ref.shape
+    assert o.shape == ref.shape and out.is_contiguous()
     assert np.array_equal(o == 0, ref == 0)
-    assert rel_max(o, ref) <= 2e-5
+    assert rel_max(o, ref) <= tol
+
+
+def test_alternate_corr_block_odd_sizes_radius3(golden):
+    import corr
+    g = golden("corr_odd_r3")
+    with torch.no_grad():
+        out = corr.AlternateCorrBlock(_t(g["fmap1"]), _t(g["fmap2"]), radius=3)(_t(g["coords_sigma4"]))
+    ref = g["out_sigma4"]
+    o = out.cpu().numpy()
+    assert np.array_equal(o == 0, ref == 0)
+    assert rel_max(o, ref) <= 1e-2
+
+
+@pytest.mark.parametrize("flow", ("smooth", "iid", "wild"))
+def test_alternate_tensor_core_vs_fp32_path_full_size(flow):
+    """BASELINE.json configs[3] shape (136x240 fmaps, D=256; B=1 here): the fused tensor-core kernel
+    against this library's fp32 per-level kernel, which is pinned to the oracle / golden vectors
+    above.  'wild' adds NaN / inf / 1e9 coordinates: same NaN pattern, no fault."""
+    import corr
+    B, D, H, W = 1, 256, 136, 240
+    gen = torch.Generator(device="cuda").manual_seed(31)
+    f1 = torch.randn(B, D, H, W, device="cuda", generator=gen)
+    f2 = torch.randn(B, D, H, W, device="cuda", generator=gen)
+    ys, xs = torch.meshgrid(torch.arange(H, device="cuda"), torch.arange(W, device="cuda"), indexing="ij")
+    grid = torch.stack([xs, ys]).float()[None]
+    if flow == "smooth":
+        low = 8 * torch.randn(B, 2, H // 8, W // 8, device="cuda", generator=gen)
+        c = grid + torch.nn.functional.interpolate(low, size=(H, W), mode="bilinear", align_corners=True)
+    else:
+        c = grid + 6 * torch.randn(B, 2, H, W, device="cuda", generator=gen)
+    if flow == "wild":
+        c[0, 0, 0, 0] = float("nan")
+        c[0, 1, 3, 5] = float("inf")
+        c[0, 0, 7, 9] = 1e9
+        c[0, 1, 9, 200] = -1e9
+        c[0, 0, 100, 100] = 3e38
+    with torch.no_grad():
+        a = corr.AlternateCorrBlock(f1, f2, precision="bf16")(c)
+        b = corr.AlternateCorrBlock(f1, f2, precision="fp32")(c)
+    assert a.shape == b.shape == (B, 324, H, W)
+    assert torch.equal(torch.isnan(a), torch.isnan(b))
+    a, b = torch.nan_to_num(a), torch.nan_to_num(b)
+    assert torch.equal(a == 0, b == 0)
+    assert (a - b).abs().max().item() <= 1e-2 * b.abs().max().item()
 
 
 def test_alt_cuda_corr_module_surface(golden):

@@ -37,6 +37,13 @@ def main():
     f2 = torch.randn(B, D, H, W, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     T = sum((H >> l) * (W >> l) for l in range(4))
+    big = torch.empty(2 << 30, dtype=torch.uint8, device="cuda")
+    ms = timeit(lambda: big.zero_(), reps=10)
+    print(f"write-only roof (torch zero_ of 2 GiB): {ms:.3f} ms  {big.numel()/ms/1e6:.0f} GB/s ({big.numel()/ms/1e6/PEAKS['hbm_gbs']:.2f} of measured copy peak)")
+    src = torch.empty(1 << 30, dtype=torch.uint8, device="cuda"); dst = torch.empty_like(src)
+    ms = timeit(lambda: dst.copy_(src), reps=10)
+    print(f"copy roof (1 GiB -> 1 GiB): {ms:.3f} ms  {2*src.numel()/ms/1e6:.0f} GB/s")
+    del big, src, dst
     for prec in ("bf16", "tf32", "fp32"):
         ms = timeit(lambda: ops.build_pyramid(f1, f2, 4, prec), reps=5 if prec == "fp32" else 10, flush=flush)
         byts = B * N * T * 4 + 2 * B * N * D * 4
