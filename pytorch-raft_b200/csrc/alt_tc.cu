@@ -17,8 +17,9 @@
 //
 //   warp 0      TMA producer  (F1 tile once, then one 8x32xC chunk of F2_l per step)
 //   warp 1      MMA issuer    (tcgen05.mma cta_group::1 kind::f16, M128 N256, 2 TMEM stages)
-//   warps 2-5   samplers      (thread = query = TMEM lane): tcgen05.ld a union row, park it in a
-//                             private shared-memory row, accumulate the taps that use it
+//   warps 2-13  samplers      (thread = query = TMEM lane, three warps per lane quarter sharing the
+//                             x taps): tcgen05.ld a union row, park it in a private shared-memory
+//                             row, accumulate the taps that use it
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -42,10 +43,12 @@ constexpr int kABytes = 128 * kKBlockBytes;     // 16 KB per k-block of the F1 t
 constexpr int kBBytes = kN * kKBlockBytes;      // 32 KB per k-block of a chunk
 constexpr int kBStages = 3;
 constexpr int kSPitch = 33;                     // floats per query row of the parking buffer
-constexpr int kAltThreads = 6 * 32;
+constexpr int kXGroups = 3;                     // sampler warps per TMEM lane quarter: x taps split 3 ways
+constexpr int kSamplerWarps = 4 * kXGroups;
+constexpr int kAltThreads = (2 + kSamplerWarps) * 32;
 constexpr int kOffB = kMaxKBlocks * kABytes;                    // 64 KB
 constexpr int kOffS = kOffB + kBStages * kBBytes;               // +96 KB
-constexpr int kOffMisc = kOffS + 128 * kSPitch * 4;             // union box, barriers, tmem slot
+constexpr int kOffMisc = kOffS + kSamplerWarps * 32 * kSPitch * 4;  // union box, barriers, tmem slot
 constexpr int kAltSmem = kOffMisc + 256;
 
 struct AltTcLevel {
@@ -91,7 +94,7 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 4);
+      mbar_init(tempty_bar(a), kSamplerWarps);
     }
     mbar_init(afull_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -116,8 +119,8 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
   const long long N1 = (long long)p.H1 * p.W1;
 
   // sampler state (thread = query)
-  const int m = threadIdx.x - 64;                       // 0..127 for warps 2..5
   const bool sampler = warp >= 2;
+  const int xg = sampler ? (warp - 2) / 4 : 0;          // which third of the x taps this warp owns
   // TMEM lanes 32*(warp%4).. belong to this warp; query index inside the tile follows the lane
   const int mq = sampler ? ((warp & 3) * 32 + lane) : 0;
   const int qy = qy0 + mq / kTileW, qx = qx0 + mq % kTileW;
@@ -127,7 +130,6 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
     cx = __ldg(p.coords + ((long long)b * 2 + 0) * N1 + (long long)qy * p.W1 + qx);
     cy = __ldg(p.coords + ((long long)b * 2 + 1) * N1 + (long long)qy * p.W1 + qx);
   }
-  (void)m;
 
   if (warp == 0 && lane == 0) {   // F1 tile: k_blocks boxes of 128 queries x 128 B, loaded once
     mbar_expect_tx(afull_bar, (uint32_t)(p.k_blocks * kABytes));
@@ -149,38 +151,55 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
     __syncthreads();
 
     // ---- tap tables of this thread's query at this level (registers) ----
-    int x0[rd], y0[rd];
-    float wx[rd], wy[rd];
+    constexpr int kXPer = (rd + kXGroups - 1) / kXGroups;   // x taps per warp group
+    int x0[kXPer], y0[rd];
+    float wx[kXPer], wy[rd];
     int my_y_lo = 0, my_y_hi = -1, my_x_lo = 0, my_x_hi = -1;
     if (valid) {
       const float lx = __fmul_rn(cx, lv.inv_pow2), ly = __fmul_rn(cy, lv.inv_pow2);
 #pragma unroll
       for (int t = 0; t < rd; ++t) {
-        const Tap a = make_tap_fast(lx, (float)(t - R), lv.sm1x, lv.invx, lv.halfx, kMode);
         const Tap c = make_tap_fast(ly, (float)(t - R), lv.sm1y, lv.invy, lv.halfy, kMode);
-        x0[t] = a.i0;
-        wx[t] = a.frac;
         y0[t] = c.i0;
         wy[t] = c.frac;
       }
-      // window clipped to the image; empty if it lies outside
-      my_x_lo = max(x0[0], 0);
-      my_x_hi = min(x0[rd - 1] + 1, lv.W - 1);
+#pragma unroll
+      for (int t = 0; t < kXPer; ++t) {
+        const int i = min(xg * kXPer + t, rd - 1);
+        const Tap a = make_tap_fast(lx, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+        x0[t] = a.i0;
+        wx[t] = a.frac;
+      }
+      // the window of the whole query (all x taps), clipped to the image; empty if it lies outside
+      const int xa = make_tap_fast(lx, (float)(-R), lv.sm1x, lv.invx, lv.halfx, kMode).i0;
+      const int xb = make_tap_fast(lx, (float)R, lv.sm1x, lv.invx, lv.halfx, kMode).i0 + 1;
+      const int q_x_lo = max(xa, 0), q_x_hi = min(xb, lv.W - 1);
       my_y_lo = max(y0[0], 0);
       my_y_hi = min(y0[rd - 1] + 1, lv.H - 1);
-      if (my_x_lo <= my_x_hi && my_y_lo <= my_y_hi) {
-        atomicMin(&ubox[0], my_x_lo);
-        atomicMin(&ubox[1], my_y_lo);
-        atomicMax(&ubox[2], my_x_hi);
-        atomicMax(&ubox[3], my_y_hi);
+      if (q_x_lo <= q_x_hi && my_y_lo <= my_y_hi) {
+        if (xg == 0) {   // one warp per lane quarter reports the query's window
+          atomicMin(&ubox[0], q_x_lo);
+          atomicMin(&ubox[1], my_y_lo);
+          atomicMax(&ubox[2], q_x_hi);
+          atomicMax(&ubox[3], my_y_hi);
+        }
+        // columns this warp's own taps touch
+        my_x_lo = max(x0[0], 0);
+        my_x_hi = min(x0[kXPer - 1] + 1, lv.W - 1);
+        if (my_x_lo > my_x_hi) my_y_hi = my_y_lo - 1;
       } else {
         my_y_hi = my_y_lo - 1;   // nothing to read for this query at this level
       }
     } else {
 #pragma unroll
       for (int t = 0; t < rd; ++t) {
-        x0[t] = y0[t] = 0;
-        wx[t] = wy[t] = 0.0f;
+        y0[t] = 0;
+        wy[t] = 0.0f;
+      }
+#pragma unroll
+      for (int t = 0; t < kXPer; ++t) {
+        x0[t] = 0;
+        wx[t] = 0.0f;
       }
     }
     __syncthreads();
@@ -228,12 +247,12 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
       }
     } else {
       // ---- samplers ----
-      float acc[rd][rd];   // [i (x tap)][j (y tap)]
+      float acc[kXPer][rd];   // [own x tap][y tap]
 #pragma unroll
-      for (int i = 0; i < rd; ++i)
+      for (int i = 0; i < kXPer; ++i)
 #pragma unroll
         for (int j = 0; j < rd; ++j) acc[i][j] = 0.0f;
-      float* srow = S_s + mq * kSPitch;
+      float* srow = S_s + ((warp - 2) * 32 + lane) * kSPitch;
       const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
       for (int c = 0; c < n_chunks; ++c, ++chunk_no) {
         const int as = chunk_no & 1;
@@ -259,7 +278,7 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
               if (north | south) {
                 const float wrow = north ? __fsub_rn(1.0f, wy[j]) : wy[j];
 #pragma unroll
-                for (int i = 0; i < rd; ++i) {
+                for (int i = 0; i < kXPer; ++i) {
                   const int c0 = x0[i] - gx0;
                   const float e = __fsub_rn(1.0f, wx[i]);
                   if ((unsigned)c0 < (unsigned)kChunkW) acc[i][j] = fmaf(srow[c0], __fmul_rn(wrow, e), acc[i][j]);
@@ -280,12 +299,16 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
         // reference's sample NaN even though every corner is out of range (0 * NaN): keep that
         float* dst = p.out + ((long long)b * p.L * rd * rd + (long long)l * rd * rd) * N1 + (long long)qy * p.W1 + qx;
 #pragma unroll
-        for (int i = 0; i < rd; ++i)
+        for (int t = 0; t < kXPer; ++t) {
+          const int i = xg * kXPer + t;
+          if (i < rd) {
 #pragma unroll
-          for (int j = 0; j < rd; ++j) {
-            const bool is_nan = (wx[i] != wx[i]) | (wy[j] != wy[j]);
-            __stcs(dst + (long long)(i * rd + j) * N1, is_nan ? __int_as_float(0x7fc00000) : acc[i][j] * p.scale);
+            for (int j = 0; j < rd; ++j) {
+              const bool is_nan = (wx[t] != wx[t]) | (wy[j] != wy[j]);
+              __stcs(dst + (long long)(i * rd + j) * N1, is_nan ? __int_as_float(0x7fc00000) : acc[t][j] * p.scale);
+            }
           }
+        }
       }
     }
   }
