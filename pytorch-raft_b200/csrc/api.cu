@@ -102,7 +102,7 @@ int raftcorr_pyramid_layout(int B, int H, int W, int num_levels, raftcorr_level*
 }
 
 int64_t raftcorr_build_workspace_bytes(int B, int D, int H, int W, int precision) {
-  if (precision == RAFTCORR_PREC_FP32) return 0;
+  if (precision == RAFTCORR_PREC_FP32 && D % 8 != 0) return 0;   // CUDA-core build, no workspace
   return build_tc_workspace_bytes(B, D, H, W, precision);
 }
 
@@ -114,10 +114,18 @@ int raftcorr_build_pyramid(const float* fmap1, const float* fmap2, int B, int D,
              D, H, W);
   RC_REQUIRE((long long)H * W <= (1 << 24), "build_pyramid: fmap too large");
   if (int rc = check_levels(levels, num_levels, H, W, "build_pyramid")) return rc;
-  if (precision == RAFTCORR_PREC_FP32)
-    return launch_build_fp32(fmap1, fmap2, B, D, H, W, num_levels, levels, (cudaStream_t)stream);
-  RC_REQUIRE(precision == RAFTCORR_PREC_BF16 || precision == RAFTCORR_PREC_TF32,
+  RC_REQUIRE(precision == RAFTCORR_PREC_FP32 || precision == RAFTCORR_PREC_BF16 || precision == RAFTCORR_PREC_TF32,
              "build_pyramid: unknown precision %d", precision);
+  if (precision == RAFTCORR_PREC_FP32) {
+    // fp32-accurate: three tf32 tensor-core passes over hi/lo splits when the layout allows it and
+    // the caller brought the workspace for them; otherwise plain fp32 FMA on the CUDA cores
+    bool tc_ok = D % 8 == 0 && workspace != nullptr && !(reinterpret_cast<uintptr_t>(workspace) & 255) &&
+                 workspace_bytes >= build_tc_workspace_bytes(B, D, H, W, precision);
+    for (int l = 0; l < num_levels && tc_ok; ++l)
+      tc_ok = !(levels[l].pitch & 3) && !(levels[l].image_stride & 3) &&
+              !(reinterpret_cast<uintptr_t>(levels[l].data) & 15);
+    if (!tc_ok) return launch_build_fp32(fmap1, fmap2, B, D, H, W, num_levels, levels, (cudaStream_t)stream);
+  }
   return launch_build_tc(fmap1, fmap2, B, D, H, W, num_levels, levels, precision, workspace,
                          workspace_bytes, (cudaStream_t)stream);
 }

@@ -43,7 +43,9 @@ constexpr int kThreads = 32 * (2 + kEpiWarps);
 struct BuildTcParams {
   int B, N, H, W, L;
   int tiles_m, tiles_y, tiles_x;
-  int k_blocks;       // ceil(D * elem_size / 128)
+  int k_blocks;       // ceil(K * elem_size / 128) per pass
+  int passes;         // 1, or 3 for the split-TF32 product (hi*hi + hi*lo + lo*hi)
+  int plain;          // 0: pyramid epilogue (8x32 pixel tiles); 1: plain C[M][N] epilogue (1x256 tiles)
   int k_elems;        // K elements per 128 B
   uint32_t idesc;
   float inv_scale;    // 1 / sqrt(D)
@@ -79,9 +81,16 @@ __device__ __forceinline__ void stage_and_store(const float* vals, const CUtenso
   }
 }
 
+// Operand maps per pass: C += A[pass] . B[pass]^T.  One pass for bf16 / tf32; three passes with
+// (A_hi,B_hi), (A_hi,B_lo), (A_lo,B_hi) give an fp32-accurate product on the tf32 tensor pipe.
+struct alignas(64) TcOperandMaps {
+  CUtensorMap a[3];
+  CUtensorMap b[3];
+};
+
 template <bool kTf32>
 __global__ void __launch_bounds__(kThreads, 1)
-build_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
                 const __grid_constant__ CUtensorMap mapL0, const __grid_constant__ CUtensorMap mapL1,
                 const __grid_constant__ CUtensorMap mapL2, const __grid_constant__ CUtensorMap mapL3,
                 const __grid_constant__ BuildTcParams p) {
@@ -107,8 +116,8 @@ build_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
       mbar_init(tempty_bar(a), 4);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&ops.a[0]) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&ops.b[0]) : "memory");
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(
@@ -132,15 +141,17 @@ build_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         const int mt = (int)((t / tiles_n) % p.tiles_m);
         const int b = (int)(t / (tiles_n * p.tiles_m));
         const int ty = nt / p.tiles_x, tx = nt - ty * p.tiles_x;
-        for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
-          const int s = it % kStages;
-          const uint32_t ph = (it / kStages) & 1;
-          mbar_wait(empty_bar(s), ph ^ 1);
-          mbar_expect_tx(full_bar(s), kStageBytes);
-          const uint32_t a_dst = smem_base + s * kStageBytes;
-          tma_load_3d(a_dst, &mapA, full_bar(s), kb * p.k_elems, mt * kBlockM, b);
-          tma_load_4d(a_dst + kBytesA, &mapB, full_bar(s), kb * p.k_elems, tx * kTileX, ty * kTileY, b);
-        }
+        const int bx = p.plain ? kBlockN : kTileX, by = p.plain ? 1 : kTileY;   // N-tile origin step
+        for (int pass = 0; pass < p.passes; ++pass)
+          for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
+            const int s = it % kStages;
+            const uint32_t ph = (it / kStages) & 1;
+            mbar_wait(empty_bar(s), ph ^ 1);
+            mbar_expect_tx(full_bar(s), kStageBytes);
+            const uint32_t a_dst = smem_base + s * kStageBytes;
+            tma_load_3d(a_dst, &ops.a[pass], full_bar(s), kb * p.k_elems, mt * kBlockM, b);
+            tma_load_4d(a_dst + kBytesA, &ops.b[pass], full_bar(s), kb * p.k_elems, tx * bx, ty * by, b);
+          }
       }
     }
   } else if (warp == 1) {
@@ -152,7 +163,7 @@ build_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
         mbar_wait(tempty_bar(as), aph ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * kBlockN;
-        for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
+        for (int kb = 0; kb < p.k_blocks * p.passes; ++kb, ++it) {
           const int s = it % kStages;
           const uint32_t ph = (it / kStages) & 1;
           mbar_wait(full_bar(s), ph);
@@ -187,6 +198,26 @@ build_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
       mbar_wait(tfull_bar(group), aph);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + group * kBlockN;
+      if (p.plain) {
+        // C[b][m][n]: this warp's 32 rows x 256 columns, eight 32x32 boxes through the staging buffers
+#pragma unroll 1
+        for (int cc = 0; cc < kBlockN / 32; ++cc) {
+          float f[32];
+          tmem_ld_x32(taddr + cc * 32, f);
+          tmem_ld_wait();
+          if (cc == kBlockN / 32 - 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(group));
+          }
+          if (!rows_live) continue;
+#pragma unroll
+          for (int c = 0; c < 32; ++c) f[c] *= p.inv_scale;
+          const int n0 = tx * kBlockN + cc * 32;
+          if (n0 < p.W) stage_and_store<32>(f, &mapL0, buf_base, nstores, lane, n0, 0, q0, b);
+        }
+        continue;
+      }
       float p1[2][16];
       float p2[2][8];
 #pragma unroll
@@ -270,14 +301,75 @@ pack_kernel(const float* __restrict__ src, T* __restrict__ dst, int D, int N) {
   }
 }
 
-size_t elem_size(int precision) { return precision == RAFTCORR_PREC_BF16 ? 2 : 4; }
+// NCHW fp32 (B, D, N) -> two K-major (B, N, D) fp32 arrays holding tf32 values: hi = rna(x),
+// lo = rna(x - hi); hi + lo reproduces x to ~2^-24, so hi*hi + hi*lo + lo*hi is an fp32-accurate
+// product on the tf32 tensor pipe.
+__global__ void __launch_bounds__(256)
+pack_split_kernel(const float* __restrict__ src, float* __restrict__ hi, float* __restrict__ lo, int D, int N) {
+  __shared__ float tile[64][33];
+  const int b = blockIdx.z;
+  const int n0 = blockIdx.x * 32, d0 = blockIdx.y * 64;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const float* s = src + (long long)b * D * N;
+  for (int c = w; c < 64; c += 8) {
+    const int d = d0 + c, n = n0 + lane;
+    tile[c][lane] = (d < D && n < N) ? __ldg(s + (long long)d * N + n) : 0.0f;
+  }
+  __syncthreads();
+  for (int px = w; px < 32; px += 8) {
+    const int n = n0 + px;
+    const int d = d0 + 2 * lane;
+    if (n >= N || d >= D) continue;
+    float h[2], l[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const float v = tile[2 * lane + k][px];
+      uint32_t r;
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+      h[k] = __uint_as_float(r);
+      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v - h[k]));
+      l[k] = __uint_as_float(r);
+    }
+    const long long o = (long long)b * N * D + (long long)n * D + d;
+    *reinterpret_cast<float2*>(hi + o) = make_float2(h[0], h[1]);
+    *reinterpret_cast<float2*>(lo + o) = make_float2(l[0], l[1]);
+  }
+}
+
+size_t elem_size(int precision) { return precision == RAFTCORR_PREC_BF16 ? 2 : 4; }  // tf32 and split-tf32 are fp32-sized
 
 int64_t align256(int64_t v) { return (v + 255) & ~(int64_t)255; }
 
 }  // namespace
 
 int64_t build_tc_workspace_bytes(int B, int D, int H, int W, int precision) {
-  return 2 * align256((int64_t)B * H * W * D * (int64_t)elem_size(precision));
+  const int64_t one = align256((int64_t)B * H * W * D * (int64_t)elem_size(precision));
+  return (precision == RAFTCORR_PREC_FP32 ? 4 : 2) * one;   // fp32: hi and lo copies of both fmaps
+}
+
+// Shared launcher of build_tc_kernel: operand maps for `passes` (A, B) pairs are already encoded.
+static int launch_tc_kernel(bool tf32, const TcOperandMaps& ops, const CUtensorMap* out_maps, const BuildTcParams& p,
+                            cudaStream_t stream) {
+  int dev = 0, sms = 0;
+  RC_CHECK_CUDA(cudaGetDevice(&dev));
+  RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const long long total = (long long)p.B * p.tiles_m * p.tiles_y * p.tiles_x;
+  if (total == 0) return 0;
+  const int grid = (int)(total < sms ? total : sms);
+  if (!tf32) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
+  } else {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<true><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
+  }
+  RC_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static uint32_t make_idesc(bool tf32) {
+  const uint32_t fmt = tf32 ? 2u : 1u;
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(kBlockN >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
 }
 
 int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W, int L,
@@ -286,6 +378,8 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   const int N = H * W;
   if (B == 0) return 0;
   const size_t es = elem_size(precision);
+  const bool split = precision == RAFTCORR_PREC_FP32;   // three tf32 passes over hi/lo operands
+  const bool tf32 = precision != RAFTCORR_PREC_BF16;
   if (D % 8 != 0) return fail(RAFTCORR_E_UNSUPPORTED, "build_pyramid: tensor-core path needs D %% 8 == 0 (D=%d)", D);
   if (ws == nullptr || ws_bytes < build_tc_workspace_bytes(B, D, H, W, precision) ||
       (reinterpret_cast<uintptr_t>(ws) & 255))
@@ -298,33 +392,47 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
                   "build_pyramid: level %d needs 16-byte aligned rows (pitch %% 4 == 0; use raftcorr_pyramid_layout)", l);
 
   char* wsb = static_cast<char*>(ws);
-  void* packA = wsb;
-  void* packB = wsb + align256((int64_t)B * N * D * (int64_t)es);
+  const int64_t one = align256((int64_t)B * N * D * (int64_t)es);
+  void* packA = wsb;            // fmap1: bf16 / tf32 / tf32-hi
+  void* packB = wsb + one;      // fmap2
+  void* packAlo = wsb + 2 * one;  // split mode only
+  void* packBlo = wsb + 3 * one;
   dim3 pgrid((N + 31) / 32, (D + 63) / 64, B);
   if (precision == RAFTCORR_PREC_BF16) {
     pack_kernel<__nv_bfloat16><<<pgrid, 256, 0, stream>>>(f1, static_cast<__nv_bfloat16*>(packA), D, N);
     pack_kernel<__nv_bfloat16><<<pgrid, 256, 0, stream>>>(f2, static_cast<__nv_bfloat16*>(packB), D, N);
-  } else {
+  } else if (!split) {
     pack_kernel<float><<<pgrid, 256, 0, stream>>>(f1, static_cast<float*>(packA), D, N);
     pack_kernel<float><<<pgrid, 256, 0, stream>>>(f2, static_cast<float*>(packB), D, N);
+  } else {
+    pack_split_kernel<<<pgrid, 256, 0, stream>>>(f1, static_cast<float*>(packA), static_cast<float*>(packAlo), D, N);
+    pack_split_kernel<<<pgrid, 256, 0, stream>>>(f2, static_cast<float*>(packB), static_cast<float*>(packBlo), D, N);
   }
   RC_CHECK_CUDA(cudaGetLastError());
 
   const CUtensorMapDataType dt =
       precision == RAFTCORR_PREC_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   const cuuint32_t k_elems = (cuuint32_t)(128 / es);
-  CUtensorMap mapA, mapB, mapL[RAFTCORR_MAX_LEVELS];
-  {
-    cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)B};
-    cuuint64_t strides[2] = {(cuuint64_t)D * es, (cuuint64_t)N * D * es};
-    cuuint32_t box[3] = {k_elems, kBlockM, 1};
-    if (int rc = encode(&mapA, dt, 3, packA, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "A")) return rc;
-  }
-  {
-    cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
-    cuuint64_t strides[3] = {(cuuint64_t)D * es, (cuuint64_t)W * D * es, (cuuint64_t)N * D * es};
-    cuuint32_t box[4] = {k_elems, kTileX, kTileY, 1};
-    if (int rc = encode(&mapB, dt, 4, packB, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "B")) return rc;
+  TcOperandMaps ops;
+  CUtensorMap mapL[RAFTCORR_MAX_LEVELS];
+  // pass p multiplies A[a_of[p]] by B[b_of[p]]: hi*hi, hi*lo, lo*hi
+  void* a_src[3] = {packA, packA, packAlo};
+  void* b_src[3] = {packB, packBlo, packB};
+  const int passes = split ? 3 : 1;
+  for (int ps = 0; ps < 3; ++ps) {
+    const int q = ps < passes ? ps : 0;
+    {
+      cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)B};
+      cuuint64_t strides[2] = {(cuuint64_t)D * es, (cuuint64_t)N * D * es};
+      cuuint32_t box[3] = {k_elems, kBlockM, 1};
+      if (int rc = encode(&ops.a[ps], dt, 3, a_src[q], dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "A")) return rc;
+    }
+    {
+      cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+      cuuint64_t strides[3] = {(cuuint64_t)D * es, (cuuint64_t)W * D * es, (cuuint64_t)N * D * es};
+      cuuint32_t box[4] = {k_elems, kTileX, kTileY, 1};
+      if (int rc = encode(&ops.b[ps], dt, 4, b_src[q], dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "B")) return rc;
+    }
   }
   const CUtensorMapSwizzle sw[4] = {CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_SWIZZLE_64B,
                                     CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_SWIZZLE_NONE};
@@ -350,27 +458,15 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   p.tiles_x = (W + kTileX - 1) / kTileX;
   p.k_elems = (int)k_elems;
   p.k_blocks = (int)((D + k_elems - 1) / k_elems);
-  const uint32_t fmt = precision == RAFTCORR_PREC_BF16 ? 1u : 2u;
-  p.idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(kBlockN >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+  p.passes = passes;
+  p.plain = 0;
+  p.idesc = make_idesc(tf32);
   p.inv_scale = 1.0f / sqrtf((float)D);
   for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
     p.Hl[l] = H >> l;
     p.Wl[l] = W >> l;
   }
-  int dev = 0, sms = 0;
-  RC_CHECK_CUDA(cudaGetDevice(&dev));
-  RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const long long total = (long long)B * p.tiles_m * p.tiles_y * p.tiles_x;
-  const int grid = (int)(total < sms ? total : sms);
-  if (precision == RAFTCORR_PREC_BF16) {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<false><<<grid, kThreads, kSmemTotal, stream>>>(mapA, mapB, mapL[0], mapL[1], mapL[2], mapL[3], p);
-  } else {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<true><<<grid, kThreads, kSmemTotal, stream>>>(mapA, mapB, mapL[0], mapL[1], mapL[2], mapL[3], p);
-  }
-  RC_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return launch_tc_kernel(tf32, ops, mapL, p, stream);
 }
 
 // ---------------------------------------------------------------------------------------------

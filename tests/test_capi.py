@@ -55,7 +55,10 @@ def test_bad_arguments_are_rejected_before_any_launch():
     assert lib.raftcorr_build_pyramid(None, None, 1, 8, 8, 8, 4, lv, 1, None, 0, None) == -1
     assert lib.raftcorr_alt_fwd(None, None, None, None, 1, 8, 8, 8, 8, 8, 4, 2, 1.0, None) == -1
     assert lib.raftcorr_build_workspace_bytes(8, 256, 55, 128, _capi.PREC_BF16) == 2 * 8 * 7040 * 256 * 2
-    assert lib.raftcorr_build_workspace_bytes(8, 256, 55, 128, _capi.PREC_FP32) == 0
+    # fp32-accurate mode: hi/lo tf32 splits of both fmaps for the tensor-core path; the CUDA-core
+    # fallback (D not a multiple of 8) needs none
+    assert lib.raftcorr_build_workspace_bytes(8, 256, 55, 128, _capi.PREC_FP32) == 4 * 8 * 7040 * 256 * 4
+    assert lib.raftcorr_build_workspace_bytes(8, 100, 55, 128, _capi.PREC_FP32) == 0
 
 
 def test_python_boundary_refuses_cpu_tensors():

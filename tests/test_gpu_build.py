@@ -76,6 +76,21 @@ def test_full_size_tensor_core_vs_fp32_path(shape, precision):
         assert (pooled - got[l]).abs().max().item() <= 2e-6 * got[l].abs().max().item()
 
 
+def test_fp32_mode_full_size_is_fp32_accurate():
+    """'fp32' precision = three tf32 tensor-core passes over hi/lo splits (csrc/build_tc.cu).  At the
+    BASELINE.json configs[1] shape it must stay within 1e-5 of max|ref| of an fp64 contraction, and the
+    CUDA-core fallback (D not a multiple of 8) must meet the same bar."""
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    for (B, D, H, W) in [(1, 256, 55, 128), (1, 100, 24, 40)]:
+        f1 = torch.randn(B, D, H, W, device="cuda", generator=gen)
+        f2 = torch.randn(B, D, H, W, device="cuda", generator=gen)
+        lv0 = ops.build_pyramid(f1, f2, 4, "fp32").views()[0].reshape(B, H * W, H * W)
+        rows = torch.arange(0, H * W, 37, device="cuda")
+        ref = torch.einsum("bdi,bdj->bij", f1.double().flatten(2)[:, :, rows], f2.double().flatten(2)) / (D ** 0.5)
+        err = (lv0[:, rows].double() - ref).abs().max().item() / ref.abs().max().item()
+        assert err <= 1e-5, (D, err)
+
+
 def test_static_corr_and_idempotence():
     """CorrBlock.corr (corr.py:52-60) shape, and two builds of the same input agree bit for bit."""
     import corr
