@@ -40,6 +40,72 @@ unpool_kernel(const __grid_constant__ GradLevels g, float* __restrict__ dC, long
   }
 }
 
+__device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  hi = __uint_as_float(r);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v - hi));
+  lo = __uint_as_float(r);
+}
+
+// Tensor-core variant of the un-pool: a 32x32 (i, j) tile of dC, written as tf32 hi/lo splits both
+// as dC[i][j] (pitch Np) and transposed as dCT[j][i], so that both backward GEMMs see K-major operands.
+__global__ void __launch_bounds__(256)
+unpool_split_kernel(const __grid_constant__ GradLevels g, float* __restrict__ c_hi, float* __restrict__ c_lo,
+                    float* __restrict__ t_hi, float* __restrict__ t_lo, int N, int Np, int W, float inv_sqrtD) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const long long base = (long long)b * N * Np;
+  for (int r = w; r < 32; r += 8) {
+    const int i = i0 + r, j = j0 + lane;
+    float v = 0.0f;
+    if (i < N && j < N) {
+      const long long q = (long long)b * N + i;
+      const int jy = j / W, jx = j - jy * W;
+      float acc = 0.0f, wgt = 1.0f;
+      for (int l = 0; l < g.L; ++l) {
+        const int yy = jy >> l, xx = jx >> l;
+        if (yy < g.H[l] && xx < g.W[l])
+          acc += wgt * __ldg(g.data[l] + q * g.istride[l] + (long long)yy * g.pitch[l] + xx);
+        wgt *= 0.25f;
+      }
+      v = acc * inv_sqrtD;
+      float hi, lo;
+      split_tf32(v, hi, lo);
+      c_hi[base + (long long)i * Np + j] = hi;
+      c_lo[base + (long long)i * Np + j] = lo;
+    }
+    tile[r][lane] = v;
+  }
+  __syncthreads();
+  for (int r = w; r < 32; r += 8) {
+    const int j = j0 + r, i = i0 + lane;
+    if (i < N && j < N) {
+      float hi, lo;
+      split_tf32(tile[lane][r], hi, lo);
+      t_hi[base + (long long)j * Np + i] = hi;
+      t_lo[base + (long long)j * Np + i] = lo;
+    }
+  }
+}
+
+// rows x N fp32 -> tf32 hi/lo with row pitch Np
+__global__ void __launch_bounds__(256)
+split_rows_kernel(const float* __restrict__ src, float* __restrict__ hi, float* __restrict__ lo, long long rows,
+                  int N, int Np) {
+  const long long total = rows * N;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const long long r = e / N;
+    const int c = (int)(e - r * N);
+    float h, l;
+    split_tf32(__ldg(src + e), h, l);
+    hi[r * Np + c] = h;
+    lo[r * Np + c] = l;
+  }
+}
+
 constexpr int kT = 64, kK = 16;
 
 // out[m, n] = sum_k A[m*a_m + k*a_k] * Bm[k*b_k + n*b_n]   (per batch), 64x64 tiles, 4x4 per thread
@@ -95,10 +161,25 @@ sgemm_strided_kernel(const float* __restrict__ A, long long a_m, long long a_k, 
 
 }  // namespace
 
+int launch_tc_gemm_split(const float* a_hi, const float* a_lo, long long a_pitch, long long a_bstride,
+                         const float* b_hi, const float* b_lo, long long b_pitch, long long b_bstride,
+                         float* out, long long o_pitch, long long o_bstride, int B, int M, int Nn, int K,
+                         cudaStream_t stream);
+bool tc_gemm_available();
+
+namespace {
+int64_t align256b(int64_t v) { return (v + 255) & ~(int64_t)255; }
+int64_t simt_ws_bytes(int B, int N) { return (int64_t)B * N * N * (int64_t)sizeof(float); }
+int64_t tc_ws_bytes(int B, int D, int N) {
+  const int64_t Np = (N + 3) & ~3;
+  return 4 * align256b((int64_t)B * N * Np * 4) + 4 * align256b((int64_t)B * D * Np * 4);
+}
+}  // namespace
+
 int64_t build_bwd_workspace_bytes(int B, int D, int H, int W) {
-  (void)D;
-  const int64_t N = (int64_t)H * W;
-  return (int64_t)B * N * N * (int64_t)sizeof(float);
+  const int N = H * W;
+  // tensor-core path (N % 4 == 0: TMA needs 16-byte row strides in d fmap) or the CUDA-core fallback
+  return (N % 4 == 0) ? tc_ws_bytes(B, D, N) : simt_ws_bytes(B, N);
 }
 
 int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, const float* f2,
@@ -106,9 +187,6 @@ int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, cons
                      cudaStream_t stream) {
   const long long N = (long long)H * W;
   if (B == 0) return 0;
-  if (ws == nullptr || ws_bytes < build_bwd_workspace_bytes(B, D, H, W))
-    return fail(RAFTCORR_E_WORKSPACE, "build_bwd: workspace %lld B < %lld B", (long long)ws_bytes,
-                (long long)build_bwd_workspace_bytes(B, D, H, W));
   GradLevels g;
   g.L = L;
   for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
@@ -119,8 +197,42 @@ int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, cons
     g.pitch[l] = glevels[s].pitch;
     g.istride[l] = glevels[s].image_stride;
   }
+  const float inv_sqrtD = 1.0f / sqrtf((float)D);
+  const bool tc = (N % 4 == 0) && tc_gemm_available() && ws != nullptr && ws_bytes >= tc_ws_bytes(B, D, (int)N) &&
+                  !(reinterpret_cast<uintptr_t>(ws) & 255) && !(reinterpret_cast<uintptr_t>(g1) & 15) &&
+                  !(reinterpret_cast<uintptr_t>(g2) & 15);
+  if (tc) {
+    // fp32-accurate tensor-core path: d f1 = dC . f2^T and d f2 = dC^T . f1^T as two split-tf32 GEMMs
+    const long long Np = (N + 3) & ~3LL;
+    char* w = static_cast<char*>(ws);
+    const int64_t cn = align256b((int64_t)B * N * Np * 4), fn = align256b((int64_t)B * D * Np * 4);
+    float* c_hi = reinterpret_cast<float*>(w);
+    float* c_lo = reinterpret_cast<float*>(w + cn);
+    float* t_hi = reinterpret_cast<float*>(w + 2 * cn);
+    float* t_lo = reinterpret_cast<float*>(w + 3 * cn);
+    float* f1_hi = reinterpret_cast<float*>(w + 4 * cn);
+    float* f1_lo = reinterpret_cast<float*>(w + 4 * cn + fn);
+    float* f2_hi = reinterpret_cast<float*>(w + 4 * cn + 2 * fn);
+    float* f2_lo = reinterpret_cast<float*>(w + 4 * cn + 3 * fn);
+    dim3 ugrid((unsigned)((N + 31) / 32), (unsigned)((N + 31) / 32), (unsigned)B);
+    unpool_split_kernel<<<ugrid, 256, 0, stream>>>(g, c_hi, c_lo, t_hi, t_lo, (int)N, (int)Np, W, inv_sqrtD);
+    RC_CHECK_CUDA(cudaGetLastError());
+    split_rows_kernel<<<148 * 8, 256, 0, stream>>>(f1, f1_hi, f1_lo, (long long)B * D, (int)N, (int)Np);
+    split_rows_kernel<<<148 * 8, 256, 0, stream>>>(f2, f2_hi, f2_lo, (long long)B * D, (int)N, (int)Np);
+    RC_CHECK_CUDA(cudaGetLastError());
+    // d f1[b][d][i] = sum_j f2[b][d][j] * dC[b][i][j]
+    if (int rc = launch_tc_gemm_split(f2_hi, f2_lo, Np, (long long)D * Np, c_hi, c_lo, Np, N * Np, g1, N,
+                                      (long long)D * N, B, D, (int)N, (int)N, stream))
+      return rc;
+    // d f2[b][d][j] = sum_i f1[b][d][i] * dC[b][i][j]
+    return launch_tc_gemm_split(f1_hi, f1_lo, Np, (long long)D * Np, t_hi, t_lo, Np, N * Np, g2, N,
+                                (long long)D * N, B, D, (int)N, (int)N, stream);
+  }
+  if (ws == nullptr || ws_bytes < simt_ws_bytes(B, (int)N))
+    return fail(RAFTCORR_E_WORKSPACE, "build_bwd: workspace %lld B < %lld B", (long long)ws_bytes,
+                (long long)simt_ws_bytes(B, (int)N));
   float* dC = static_cast<float*>(ws);
-  unpool_kernel<<<148 * 8, 256, 0, stream>>>(g, dC, (long long)B * N, H, W, 1.0f / sqrtf((float)D));
+  unpool_kernel<<<148 * 8, 256, 0, stream>>>(g, dC, (long long)B * N, H, W, inv_sqrtD);
   RC_CHECK_CUDA(cudaGetLastError());
   dim3 grid((unsigned)((N + kT - 1) / kT), (unsigned)((D + kT - 1) / kT), (unsigned)B);
   // d f1[d, i] = sum_j f2[d, j] * dC[i, j]

@@ -469,6 +469,72 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   return launch_tc_kernel(tf32, ops, mapL, p, stream);
 }
 
+// Batched fp32-accurate GEMM on the tf32 tensor pipe (plain epilogue), used by build_bwd.cu:
+//   C[b][m][n] = sum_k A[b][m][k] * B[b][n][k]      A = a_hi + a_lo, B = b_hi + b_lo (tf32 values)
+// All operands are K-major fp32 with row pitches / batch strides in elements; pitches and o_pitch
+// must be multiples of 4 (16-byte TMA strides).  K and N tails are zero-filled / clipped by TMA.
+int launch_tc_gemm_split(const float* a_hi, const float* a_lo, long long a_pitch, long long a_bstride,
+                         const float* b_hi, const float* b_lo, long long b_pitch, long long b_bstride,
+                         float* out, long long o_pitch, long long o_bstride, int B, int M, int Nn, int K,
+                         cudaStream_t stream) {
+  if (B == 0 || M == 0 || Nn == 0) return 0;
+  if ((a_pitch | b_pitch | o_pitch | a_bstride | b_bstride | o_bstride) & 3)
+    return fail(RAFTCORR_E_UNSUPPORTED, "tc_gemm: pitches must be multiples of 4 elements");
+  TcOperandMaps ops;
+  const float* a_src[3] = {a_hi, a_hi, a_lo};
+  const float* b_src[3] = {b_hi, b_lo, b_hi};
+  for (int ps = 0; ps < 3; ++ps) {
+    {
+      cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)M, (cuuint64_t)B};
+      cuuint64_t strides[2] = {(cuuint64_t)a_pitch * 4, (cuuint64_t)a_bstride * 4};
+      cuuint32_t box[3] = {32, kBlockM, 1};
+      if (int rc = encode(&ops.a[ps], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(a_src[ps]), dims, strides,
+                          box, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A"))
+        return rc;
+    }
+    {
+      cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)Nn, 1, (cuuint64_t)B};
+      cuuint64_t strides[3] = {(cuuint64_t)b_pitch * 4, (cuuint64_t)b_bstride * 4, (cuuint64_t)b_bstride * 4};
+      cuuint32_t box[4] = {32, kBlockN, 1, 1};
+      if (int rc = encode(&ops.b[ps], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(b_src[ps]), dims, strides,
+                          box, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B"))
+        return rc;
+    }
+  }
+  CUtensorMap outm[RAFTCORR_MAX_LEVELS];
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)Nn, 1, (cuuint64_t)M, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)o_pitch * 4, (cuuint64_t)o_pitch * 4, (cuuint64_t)o_bstride * 4};
+    cuuint32_t box[4] = {32, 1, 32, 1};
+    for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l)
+      if (int rc = encode(&outm[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, dims, strides, box,
+                          CU_TENSOR_MAP_SWIZZLE_128B, "gemm C"))
+        return rc;
+  }
+  BuildTcParams p;
+  p.B = B;
+  p.N = M;     // rows of C (TMEM lanes)
+  p.H = 1;
+  p.W = Nn;    // columns of C
+  p.L = 1;
+  p.tiles_m = (M + kBlockM - 1) / kBlockM;
+  p.tiles_y = 1;
+  p.tiles_x = (Nn + kBlockN - 1) / kBlockN;
+  p.k_elems = 32;
+  p.k_blocks = (K + 31) / 32;
+  p.passes = 3;
+  p.plain = 1;
+  p.idesc = make_idesc(true);
+  p.inv_scale = 1.0f;
+  for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
+    p.Hl[l] = 1;
+    p.Wl[l] = Nn;
+  }
+  return launch_tc_kernel(true, ops, outm, p, stream);
+}
+
+bool tc_gemm_available() { return get_encode() != nullptr; }
+
 // ---------------------------------------------------------------------------------------------
 // Allocation-free variant of the tensor-core build.
 //
