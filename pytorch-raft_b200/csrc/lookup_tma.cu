@@ -291,13 +291,34 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
                 const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
                 const float* f = buf + l * (kSlotBytes / 4) + (a.i0 + wv[l].x) - wv[l].y * kBoxW;
                 float* o = out_s + (l * rd2 + ti * rd) * kOutPitch + qi;
+                // this lane's y taps; when their rows are consecutive (no floor flip inside the
+                // group, the usual case) adjacent samples share a row: 8 loads instead of 12
+                Tap cj[C::kJPer];
 #pragma unroll
-                for (int jj = 0; jj < C::kJPer; ++jj) {
-                  const int j = (tj0 + jj < rd) ? tj0 + jj : rd - 1;   // clamp keeps the loads in range
-                  const Tap c = ty[j];
-                  const float* gp = f + c.i0 * kBoxW;
-                  const float v = bilinear_combine(gp[0], gp[1], gp[kBoxW], gp[kBoxW + 1], a.frac, c.frac);
-                  if (tj0 + jj < rd) o[j * kOutPitch] = v;
+                for (int jj = 0; jj < C::kJPer; ++jj) cj[jj] = ty[(tj0 + jj < rd) ? tj0 + jj : rd - 1];
+                bool chain = true;
+#pragma unroll
+                for (int jj = 1; jj < C::kJPer; ++jj) chain &= cj[jj].i0 == cj[jj - 1].i0 + 1;
+                if (__all_sync(__activemask(), chain)) {
+                  const float* gp = f + cj[0].i0 * kBoxW;
+                  float r0[C::kJPer + 1], r1[C::kJPer + 1];
+#pragma unroll
+                  for (int t = 0; t <= C::kJPer; ++t) {
+                    r0[t] = gp[t * kBoxW];
+                    r1[t] = gp[t * kBoxW + 1];
+                  }
+#pragma unroll
+                  for (int jj = 0; jj < C::kJPer; ++jj) {
+                    const float v = bilinear_combine(r0[jj], r1[jj], r0[jj + 1], r1[jj + 1], a.frac, cj[jj].frac);
+                    if (tj0 + jj < rd) o[(tj0 + jj) * kOutPitch] = v;
+                  }
+                } else {
+#pragma unroll
+                  for (int jj = 0; jj < C::kJPer; ++jj) {
+                    const float* gp = f + cj[jj].i0 * kBoxW;
+                    const float v = bilinear_combine(gp[0], gp[1], gp[kBoxW], gp[kBoxW + 1], a.frac, cj[jj].frac);
+                    if (tj0 + jj < rd) o[(tj0 + jj) * kOutPitch] = v;
+                  }
                 }
               }
             }
