@@ -42,7 +42,7 @@ constexpr int kMaxKBlocks = 4;                  // C <= 256
 constexpr int kABytes = 128 * kKBlockBytes;     // 16 KB per k-block of the F1 tile
 constexpr int kBBytes = kN * kKBlockBytes;      // 32 KB per k-block of a chunk
 constexpr int kBStages = 3;
-constexpr int kSPitch = 33;                     // floats per query row of the parking buffer
+constexpr int kSPitch = 36;                     // floats per query row of the parking buffer (16-byte rows)
 constexpr int kXGroups = 3;                     // sampler warps per TMEM lane quarter: x taps split 3 ways
 constexpr int kSamplerWarps = 4 * kXGroups;
 constexpr int kAltThreads = (2 + kSamplerWarps) * 32;
@@ -270,21 +270,29 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
           tmem_ld_wait();
           if (need) {
 #pragma unroll
-            for (int k = 0; k < kChunkW; ++k) srow[k] = f[k];
+            for (int k = 0; k < kChunkW; k += 4)
+              *reinterpret_cast<float4*>(srow + k) = make_float4(f[k], f[k + 1], f[k + 2], f[k + 3]);
+            // horizontal interpolation of this row at the warp's x taps (columns of a tap that fall
+            // into a neighbouring chunk contribute there: the sum over chunks is the full value)
+            float h[kXPer];
+#pragma unroll
+            for (int i = 0; i < kXPer; ++i) {
+              const int c0 = x0[i] - gx0;
+              const float v0 = (unsigned)c0 < (unsigned)kChunkW ? srow[c0] : 0.0f;
+              const float v1 = (unsigned)(c0 + 1) < (unsigned)kChunkW ? srow[c0 + 1] : 0.0f;
+              h[i] = fmaf(v1, wx[i], __fmul_rn(v0, __fsub_rn(1.0f, wx[i])));
+            }
             // the row is the north row of taps with y0 == gy and the south row of taps with y0+1 == gy
 #pragma unroll
             for (int j = 0; j < rd; ++j) {
-              const bool north = y0[j] == gy, south = y0[j] + 1 == gy;
-              if (north | south) {
-                const float wrow = north ? __fsub_rn(1.0f, wy[j]) : wy[j];
+              if (y0[j] == gy) {
+                const float s_ = __fsub_rn(1.0f, wy[j]);
 #pragma unroll
-                for (int i = 0; i < kXPer; ++i) {
-                  const int c0 = x0[i] - gx0;
-                  const float e = __fsub_rn(1.0f, wx[i]);
-                  if ((unsigned)c0 < (unsigned)kChunkW) acc[i][j] = fmaf(srow[c0], __fmul_rn(wrow, e), acc[i][j]);
-                  if ((unsigned)(c0 + 1) < (unsigned)kChunkW)
-                    acc[i][j] = fmaf(srow[c0 + 1], __fmul_rn(wrow, wx[i]), acc[i][j]);
-                }
+                for (int i = 0; i < kXPer; ++i) acc[i][j] = fmaf(h[i], s_, acc[i][j]);
+              }
+              if (y0[j] + 1 == gy) {
+#pragma unroll
+                for (int i = 0; i < kXPer; ++i) acc[i][j] = fmaf(h[i], wy[j], acc[i][j]);
               }
             }
           }
