@@ -302,7 +302,7 @@ def main():
                        build_precision=args.precision or "bf16", encoders="stock PyTorch/cuDNN fp32"),
         "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": (3 + ITERS) * args.steps * n_gpus,
+        "gpu_launches": (2 + ITERS) * args.steps * n_gpus,   # pack + tcgen05 build + 12 lookups per step
         "roofline": {"kernel": "lookup_fwd_tma_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic_per_launch(),
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": queries * LOOKUP_BYTES_PER_QUERY,

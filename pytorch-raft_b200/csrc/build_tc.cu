@@ -301,6 +301,49 @@ pack_kernel(const float* __restrict__ src, T* __restrict__ dst, int D, int N) {
   }
 }
 
+// Both feature maps in one launch, bf16: NCHW fp32 (B, D, N) -> K-major (B, N, D).  64 channels x 64
+// pixels per block, 16-byte loads along pixels and 16-byte stores along channels.
+__global__ void __launch_bounds__(256)
+pack2_bf16_kernel(const float* __restrict__ src1, const float* __restrict__ src2, __nv_bfloat16* __restrict__ dst1,
+                  __nv_bfloat16* __restrict__ dst2, int D, int N) {
+  __shared__ float tile[64][65];
+  const int b = blockIdx.z >> 1;
+  const float* s = ((blockIdx.z & 1) ? src2 : src1) + (long long)b * D * N;
+  __nv_bfloat16* o = ((blockIdx.z & 1) ? dst2 : dst1) + (long long)b * N * D;
+  const int n0 = blockIdx.x * 64, d0 = blockIdx.y * 64;
+  const int tid = threadIdx.x;
+  if ((N & 3) == 0) {
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int e = tid + 256 * it;          // 1024 float4 per tile
+      const int c = e >> 4, p4 = (e & 15) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (d0 + c < D && n0 + p4 < N) v = __ldg(reinterpret_cast<const float4*>(s + (long long)(d0 + c) * N + n0 + p4));
+      tile[c][p4] = v.x;
+      tile[c][p4 + 1] = v.y;
+      tile[c][p4 + 2] = v.z;
+      tile[c][p4 + 3] = v.w;
+    }
+  } else {
+    for (int e = tid; e < 64 * 64; e += 256) {
+      const int c = e >> 6, px = e & 63;
+      tile[c][px] = (d0 + c < D && n0 + px < N) ? __ldg(s + (long long)(d0 + c) * N + n0 + px) : 0.0f;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int px = (tid >> 3) + 32 * it, q = tid & 7;   // 8 channels (16 B) per thread
+    const int n = n0 + px, d = d0 + 8 * q;
+    if (n < N && d < D) {                              // D % 8 == 0 (checked by the launcher)
+      __nv_bfloat162 h[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(tile[8 * q + 2 * k][px], tile[8 * q + 2 * k + 1][px]);
+      *reinterpret_cast<uint4*>(o + (long long)n * D + d) = *reinterpret_cast<uint4*>(h);
+    }
+  }
+}
+
 // NCHW fp32 (B, D, N) -> two K-major (B, N, D) fp32 arrays holding tf32 values: hi = rna(x),
 // lo = rna(x - hi); hi + lo reproduces x to ~2^-24, so hi*hi + hi*lo + lo*hi is an fp32-accurate
 // product on the tf32 tensor pipe.
@@ -399,8 +442,9 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   void* packBlo = wsb + 3 * one;
   dim3 pgrid((N + 31) / 32, (D + 63) / 64, B);
   if (precision == RAFTCORR_PREC_BF16) {
-    pack_kernel<__nv_bfloat16><<<pgrid, 256, 0, stream>>>(f1, static_cast<__nv_bfloat16*>(packA), D, N);
-    pack_kernel<__nv_bfloat16><<<pgrid, 256, 0, stream>>>(f2, static_cast<__nv_bfloat16*>(packB), D, N);
+    dim3 g2((N + 63) / 64, (D + 63) / 64, 2 * B);
+    pack2_bf16_kernel<<<g2, 256, 0, stream>>>(f1, f2, static_cast<__nv_bfloat16*>(packA),
+                                              static_cast<__nv_bfloat16*>(packB), D, N);
   } else if (!split) {
     pack_kernel<float><<<pgrid, 256, 0, stream>>>(f1, static_cast<float*>(packA), D, N);
     pack_kernel<float><<<pgrid, 256, 0, stream>>>(f2, static_cast<float*>(packB), D, N);

@@ -3,17 +3,18 @@
 // Same arithmetic as lookup.cu (reference core/corr.py:29-50 + core/utils/utils.py:57-65 +
 // ATen grid_sampler_2d), different data movement.  The lookup is a gather: each query reads a
 // ~10x10 window out of its OWN H_l x W_l image at each of the 4 levels — 40-byte row pieces
-// scattered over gigabytes.  Instead of having warps chase those rows through the LSU, one
-// producer warp turns every (query, level) window into ONE TMA tensor-tile load
-// (cp.async.bulk.tensor.3d, box 12 x {10,11,12} x 1 out of the (W_l, H_l, B*N) level tensor):
-// the TMA engine generates the row requests, zero-fills everything outside the image (that IS
-// grid_sample's zero padding) and signals an mbarrier.  Sixteen consumer warps form the
-// (2r+1)^2 x 4 bilinear samples from shared memory while the next tile's windows are in flight
-// (two stages of 32 queries x 4 levels), then write the NCHW tile as full 128-byte rows.
+// scattered over gigabytes.  Instead of having warps chase those rows through the LSU, every
+// (query, level) window becomes ONE TMA tensor-tile load (cp.async.bulk.tensor.3d, box
+// 16 x {10,11,12} x 1 out of the (W_l, H_l, B*N) level tensor): the TMA engine generates the row
+// requests, zero-fills everything outside the image (that IS grid_sample's zero padding) and
+// signals an mbarrier.
 //
-//   CTA = 1 SM, persistent over tiles of 32 consecutive-x queries
-//   warp 16        producer: coords -> box origins -> 128 TMA loads per tile
-//   warps 0..15    consumers: tap tables, bilinear samples, transposed store
+//   CTA = 1 SM, persistent over tiles of 32 consecutive-x queries (two units of 16 queries)
+//   warps 16..23   staging: per query the 72 tap coordinates (exact fp32 op sequence), the window
+//                  of each level, 4 TMA loads into the ring slot of the sampling warp they feed
+//   warps 0..15    sampling: one query per warp per unit out of a 3-slot ring (full/empty
+//                  mbarriers), 81 x 4 bilinear samples from shared memory, then the CTA writes the
+//                  NCHW tile as full 128-byte rows
 #include <string.h>
 
 #include <atomic>
