@@ -1,0 +1,71 @@
+"""Drop-in hygiene: the library is called from one Python thread per GPU under
+nn.DataParallel and must honour the caller's stream; it must also be capturable in a CUDA graph
+by a caller who wants to remove launch overhead from RAFT's refinement loop."""
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from raftcorr_b200 import ops
+from helpers import coords_for, pyramid_from_numpy
+
+pytestmark = pytest.mark.gpu
+
+
+def test_concurrent_threads_and_streams_same_device():
+    gen = torch.Generator().manual_seed(13)
+    cases = []
+    for k, (B, H, W) in enumerate([(1, 24, 40), (2, 16, 36), (1, 31, 33), (1, 24, 40)]):
+        levels = [torch.randn(B * H * W, 1, H >> l, W >> l, generator=gen).numpy() for l in range(4)]
+        c = coords_for("sigma4", B, H, W, gen)
+        cases.append((levels, c, oracle.lookup(levels, c.numpy(), 4), (B, H, W)))
+    results, errors = [None] * len(cases), []
+
+    def worker(idx):
+        try:
+            levels, c, _, (B, H, W) = cases[idx]
+            stream = torch.cuda.Stream()
+            with torch.cuda.stream(stream):
+                pyr = pyramid_from_numpy(levels, B, H, W)
+                cd = c.cuda()
+                for _ in range(25):          # many calls: exercises the tensor-map cache under contention
+                    out = ops.lookup(pyr, cd, 4, "aten_cpu")
+                stream.synchronize()
+                results[idx] = out.cpu().numpy()
+        except Exception as exc:   # pragma: no cover
+            errors.append(exc)
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(len(cases))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for got, (_, _, want, _) in zip(results, cases):
+        assert np.array_equal(got, want)
+
+
+def test_build_and_lookup_are_cuda_graph_capturable():
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    f1 = torch.randn(2, 64, 24, 40, device="cuda", generator=gen)
+    f2 = torch.randn(2, 64, 24, 40, device="cuda", generator=gen)
+    c = coords_for("sigma4", 2, 24, 40, torch.Generator().manual_seed(1)).cuda()
+    eager = ops.lookup(ops.build_pyramid(f1, f2, 4, "bf16"), c, 4)   # also warms one-time set-up
+    g = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            pyr = ops.build_pyramid(f1, f2, 4, "bf16")
+            out = ops.lookup(pyr, c, 4)
+    torch.cuda.current_stream().wait_stream(side)
+    out.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, eager)
+    f1.mul_(2.0)               # the graph re-reads its inputs: outputs follow them
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.allclose(out, 2.0 * eager, rtol=2e-2, atol=1e-3)
