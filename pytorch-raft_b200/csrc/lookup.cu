@@ -19,10 +19,12 @@ namespace {
 
 using namespace lk;
 
+// kR > 0 fixes the radius at compile time (no run-time integer divisions); kR == 0 reads p.r
+template <int kR>
 __global__ void __launch_bounds__(kWarps * 32)
 lookup_fwd_kernel(const __grid_constant__ LookupParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int rd = 2 * p.r + 1;
+  const int rd = kR > 0 ? 2 * kR + 1 : 2 * p.r + 1;
   const int rd2 = rd * rd;
   const int C = p.L * rd2;
   float* out_s = reinterpret_cast<float*>(smem_raw);                    // [C][kOutPitch]
@@ -166,11 +168,15 @@ int launch_lookup_fwd(const raftcorr_level* levels, int L, const float* coords, 
                       (size_t)kWarps * RAFTCORR_MAX_LEVELS * kFootN * sizeof(float) +
                       (size_t)kWarps * RAFTCORR_MAX_LEVELS * 2 * kMaxRd * sizeof(Tap);
   static_assert(sizeof(Tap) == 8, "Tap is an (int, float) pair");
-  RC_CHECK_CUDA(cudaFuncSetAttribute(lookup_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem));
   const long long tiles = (long long)B * H * p.tiles_x;
   if (tiles == 0) return 0;
-  lookup_fwd_kernel<<<(unsigned)tiles, kWarps * 32, smem, stream>>>(p);
+  auto launch = [&](auto kernel) -> int {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kernel<<<(unsigned)tiles, kWarps * 32, smem, stream>>>(p);
+    return 0;
+  };
+  if (int rc = (r == 4 ? launch(lookup_fwd_kernel<4>) : r == 3 ? launch(lookup_fwd_kernel<3>) : launch(lookup_fwd_kernel<0>)))
+    return rc;
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -198,10 +204,11 @@ struct LookupBwdParams {
   int B, H, W, L, r, mode, tiles_x, want_levels, want_coords;
 };
 
+template <int kR>
 __global__ void __launch_bounds__(kWarps * 32)
 lookup_bwd_kernel(const __grid_constant__ LookupBwdParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int rd = 2 * p.r + 1;
+  const int rd = kR > 0 ? 2 * kR + 1 : 2 * p.r + 1;
   const int rd2 = rd * rd;
   const int C = p.L * rd2;
   float* g_s = reinterpret_cast<float*>(smem_raw);  // [C][kOutPitch]
@@ -320,11 +327,15 @@ int launch_lookup_bwd(const raftcorr_level* levels, const raftcorr_level* glevel
   const int rd = 2 * r + 1;
   const size_t smem = (size_t)L * rd * rd * kOutPitch * sizeof(float) +
                       (size_t)kWarps * RAFTCORR_MAX_LEVELS * 2 * kMaxRd * sizeof(Tap);
-  RC_CHECK_CUDA(cudaFuncSetAttribute(lookup_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem));
   const long long tiles = (long long)B * H * p.tiles_x;
   if (tiles == 0) return 0;
-  lookup_bwd_kernel<<<(unsigned)tiles, kWarps * 32, smem, stream>>>(p);
+  auto launch = [&](auto kernel) -> int {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kernel<<<(unsigned)tiles, kWarps * 32, smem, stream>>>(p);
+    return 0;
+  };
+  if (int rc = (r == 4 ? launch(lookup_bwd_kernel<4>) : r == 3 ? launch(lookup_bwd_kernel<3>) : launch(lookup_bwd_kernel<0>)))
+    return rc;
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
