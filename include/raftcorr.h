@@ -100,6 +100,14 @@ int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B
 int raftcorr_lookup_fwd(const raftcorr_level* levels, int num_levels, const float* coords,
                         float* out, int B, int H, int W, int radius, int coord_mode, void* stream);
 
+/* Same samples, channels-last: out is (B, H, W, L*(2r+1)^2), i.e. a (B, C, H, W) tensor in PyTorch's
+ * channels_last memory format.  The consumer of the lookup, BasicMotionEncoder.convc1 (a 1x1 convolution,
+ * core/update.py:82-90), is run by cuDNN in NHWC anyway; writing a query's C samples contiguously also
+ * spares the kernel its shared-memory transpose.  Values are identical to
+ * raftcorr_lookup_fwd. */
+int raftcorr_lookup_fwd_nhwc(const raftcorr_level* levels, int num_levels, const float* coords,
+                             float* out, int B, int H, int W, int radius, int coord_mode, void* stream);
+
 /* Backward of (2) (the reference gets it from autograd: GridSampler2DBackward0, SURVEY.md §8
  * a-10).  grad_levels[l] must be zero-filled by the caller and are accumulated into with
  * atomics (several lookups may accumulate into the same buffers).  grad_coords (B,2,H,W) may be

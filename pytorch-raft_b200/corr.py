@@ -28,10 +28,14 @@ class CorrBlock:
     """core/corr.py:12-60.  ``corr_pyramid`` keeps the reference's shapes
     ``(B*H*W, 1, H_l, W_l)`` (strided views: rows are padded to 16 bytes for TMA)."""
 
-    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, *, precision=None, coord_mode=None):
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=4, *, precision=None, coord_mode=None,
+                 channels_last=False):
         self.num_levels = num_levels
         self.radius = radius
         self._coord_mode = ops.resolve_coord_mode(coord_mode)
+        # channels_last=True returns the lookup in torch.channels_last memory format (same shape and
+        # values; cuDNN runs the consuming 1x1 convolution in NHWC anyway).  Inference path only.
+        self._channels_last = bool(channels_last)
         self._holder = {}
         self._token = None
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
@@ -50,7 +54,7 @@ class CorrBlock:
             if token is None:
                 token = torch.zeros(1, dtype=torch.float32, device=coords.device)
             return ops.LookupFn.apply(coords, token, self._holder, self.radius, self._coord_mode)
-        return ops.lookup(self._holder["pyr"], coords, self.radius, self._coord_mode)
+        return ops.lookup(self._holder["pyr"], coords, self.radius, self._coord_mode, self._channels_last)
 
     @staticmethod
     def corr(fmap1, fmap2, *, precision=None):

@@ -30,7 +30,7 @@ int cuda_fail(cudaError_t err, const char* what) {
 
 // launchers implemented in the kernel files
 int launch_lookup_fwd(const raftcorr_level* levels, int L, const float* coords, float* out, int B,
-                      int H, int W, int r, int mode, cudaStream_t stream);
+                      int H, int W, int r, int mode, int nhwc, cudaStream_t stream);
 int launch_lookup_bwd(const raftcorr_level* levels, const raftcorr_level* glevels, int L,
                       const float* coords, const float* gout, float* gcoords, int B, int H, int W,
                       int r, int mode, cudaStream_t stream);
@@ -152,7 +152,18 @@ int raftcorr_lookup_fwd(const raftcorr_level* levels, int num_levels, const floa
   RC_REQUIRE(radius >= 0 && radius <= 4, "lookup_fwd: radius=%d not in [0,4]", radius);
   RC_REQUIRE(valid_mode(coord_mode), "lookup_fwd: coord_mode=%d", coord_mode);
   if (int rc = check_levels(levels, num_levels, H, W, "lookup_fwd")) return rc;
-  return launch_lookup_fwd(levels, num_levels, coords, out, B, H, W, radius, coord_mode,
+  return launch_lookup_fwd(levels, num_levels, coords, out, B, H, W, radius, coord_mode, 0,
+                           (cudaStream_t)stream);
+}
+
+int raftcorr_lookup_fwd_nhwc(const raftcorr_level* levels, int num_levels, const float* coords,
+                             float* out, int B, int H, int W, int radius, int coord_mode, void* stream) {
+  RC_REQUIRE(coords && out, "lookup_fwd_nhwc: coords/out is NULL");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "lookup_fwd_nhwc: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(radius >= 0 && radius <= 4, "lookup_fwd_nhwc: radius=%d not in [0,4]", radius);
+  RC_REQUIRE(valid_mode(coord_mode), "lookup_fwd_nhwc: coord_mode=%d", coord_mode);
+  if (int rc = check_levels(levels, num_levels, H, W, "lookup_fwd_nhwc")) return rc;
+  return launch_lookup_fwd(levels, num_levels, coords, out, B, H, W, radius, coord_mode, 1,
                            (cudaStream_t)stream);
 }
 

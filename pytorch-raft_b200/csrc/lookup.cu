@@ -130,6 +130,14 @@ lookup_fwd_kernel(const __grid_constant__ LookupParams p) {
   }
   __syncthreads();
 
+  if (p.nhwc) {   // (B, H, W, C): each query's C samples are contiguous
+    for (int qi = warp; qi < kTileQ; qi += kWarps) {
+      if (x0 + qi >= p.W) break;
+      float* dst = p.out + ((long long)b * N + (long long)y * p.W + x0 + qi) * C;
+      for (int c = lane; c < C; c += 32) __stcs(dst + c, out_s[c * kOutPitch + qi]);
+    }
+    return;
+  }
   // coalesced NCHW store: one 128-byte row (32 consecutive x) per warp instruction
   const int x = x0 + lane;
   if (x < p.W) {
@@ -141,13 +149,13 @@ lookup_fwd_kernel(const __grid_constant__ LookupParams p) {
 }  // namespace
 
 int launch_lookup_fwd_tma(const raftcorr_level* levels, int L, const float* coords, float* out, int B,
-                          int H, int W, int r, int mode, cudaStream_t stream);
+                          int H, int W, int r, int mode, int nhwc, cudaStream_t stream);
 
 int launch_lookup_fwd(const raftcorr_level* levels, int L, const float* coords, float* out, int B,
-                      int H, int W, int r, int mode, cudaStream_t stream) {
+                      int H, int W, int r, int mode, int nhwc, cudaStream_t stream) {
   // Rows on 16-byte boundaries (raftcorr_pyramid_layout) and r in {3,4}: TMA-gather pipeline.
   // Any other strides / radii: the generic-stride kernel below (same arithmetic).
-  const int rc = launch_lookup_fwd_tma(levels, L, coords, out, B, H, W, r, mode, stream);
+  const int rc = launch_lookup_fwd_tma(levels, L, coords, out, B, H, W, r, mode, nhwc, stream);
   if (rc != 1) return rc;
   LookupParams p;
   for (int l = 0; l < L; ++l)
@@ -156,6 +164,7 @@ int launch_lookup_fwd(const raftcorr_level* levels, int L, const float* coords, 
   for (int l = L; l < RAFTCORR_MAX_LEVELS; ++l) p.lv[l] = p.lv[0];
   p.coords = coords;
   p.out = out;
+  p.nhwc = nhwc;
   p.B = B;
   p.H = H;
   p.W = W;

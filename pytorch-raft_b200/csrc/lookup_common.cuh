@@ -19,6 +19,7 @@ struct LookupParams {
   const float* coords;
   float* out;
   int B, H, W, L, r, mode, tiles_x;
+  int nhwc;   // 1: out is (B, H, W, C)
 };
 
 struct Tap {

@@ -55,6 +55,7 @@ struct LookupTmaParams {
   float* out;
   int B, H, W, tiles_x;
   long long tiles;
+  int nhwc;   // 1: out is (B, H, W, C) - each query's C samples contiguous, no transpose needed
 };
 
 template <int R, int L>
@@ -93,7 +94,8 @@ __device__ __noinline__ float sample_direct(const LevelDev& lv, long long q, Tap
 // fp32 spacing breaks the tap pattern): per-sample choice between the staged box and global memory.
 template <int R, int L>
 __device__ __noinline__ void sample_query_slow(const LookupTmaParams& p, const Tap* tab, const int4* wv,
-                                               const float* buf, float* out_s, long long q, int qi, int lane) {
+                                               const float* buf, float* out_s, long long q, int qi, int lane,
+                                               int out_stride) {
   constexpr int rd = 2 * R + 1, rd2 = rd * rd;
   for (int l = 0; l < L; ++l) {
     const Tap* tx = tab + (l * 2 + 0) * kMaxRd;
@@ -108,12 +110,12 @@ __device__ __noinline__ void sample_query_slow(const LookupTmaParams& p, const T
       } else {
         v = sample_direct(p.lv[l], q, a, c);
       }
-      out_s[(l * rd2 + k) * kOutPitch + qi] = v;
+      out_s[(l * rd2 + k) * out_stride + qi] = v;
     }
   }
 }
 
-template <int R, int L, int kMode>
+template <int R, int L, int kMode, bool kNhwc>
 __global__ void __launch_bounds__(kThreadsTma, 1)
 lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_constant__ LookupTmaMaps maps) {
   using C = Cfg<R, L>;
@@ -276,6 +278,10 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
           phases ^= 1u << slot;
           const Tap* tab = tab_w + slot * kTabEntries;
           const float* buf = reinterpret_cast<const float*>(smem + (slot * kWarpsTma + warp) * kWarpBufBytes);
+          const long long qglob = (long long)cur.b * N + (long long)cur.y * p.W + x;
+          // NCHW: park in the transposing tile; NHWC: the query's C samples are contiguous in global memory
+          float* obase = kNhwc ? p.out + qglob * C::kChannels : out_s + qi;
+          constexpr int ostride = kNhwc ? 1 : kOutPitch;
           int4 wv[L];
           int all_fast = 1;
 #pragma unroll
@@ -291,7 +297,7 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
                 const Tap a = tab[(l * 2 + 0) * kMaxRd + ti];
                 const Tap* ty = tab + (l * 2 + 1) * kMaxRd;
                 const float* f = buf + l * (kSlotBytes / 4) + (a.i0 + wv[l].x) - wv[l].y * kBoxW;
-                float* o = out_s + (l * rd2 + ti * rd) * kOutPitch + qi;
+                float* o = obase + (l * rd2 + ti * rd) * ostride;
                 // this lane's y taps; when their rows are consecutive (no floor flip inside the
                 // group, the usual case) adjacent samples share a row: 8 loads instead of 12
                 Tap cj[C::kJPer];
@@ -311,20 +317,21 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
 #pragma unroll
                   for (int jj = 0; jj < C::kJPer; ++jj) {
                     const float v = bilinear_combine(r0[jj], r1[jj], r0[jj + 1], r1[jj + 1], a.frac, cj[jj].frac);
-                    if (tj0 + jj < rd) o[(tj0 + jj) * kOutPitch] = v;
+                    if (tj0 + jj < rd) o[(tj0 + jj) * ostride] = v;
                   }
                 } else {
 #pragma unroll
                   for (int jj = 0; jj < C::kJPer; ++jj) {
                     const float* gp = f + cj[jj].i0 * kBoxW;
                     const float v = bilinear_combine(gp[0], gp[1], gp[kBoxW], gp[kBoxW + 1], a.frac, cj[jj].frac);
-                    if (tj0 + jj < rd) o[(tj0 + jj) * kOutPitch] = v;
+                    if (tj0 + jj < rd) o[(tj0 + jj) * ostride] = v;
                   }
                 }
               }
             }
           } else {
-            sample_query_slow<R, L>(p, tab, win_w + slot * RAFTCORR_MAX_LEVELS, buf, out_s, (long long)cur.b * N + (long long)cur.y * p.W + x, qi, lane);
+            sample_query_slow<R, L>(p, tab, win_w + slot * RAFTCORR_MAX_LEVELS, buf, kNhwc ? obase : out_s, qglob,
+                                    kNhwc ? 0 : qi, lane, ostride);
           }
           __syncwarp();
           if (lane == 0) mbar_arrive(empty_bar(warp, slot));   // ring slot may be refilled
@@ -332,6 +339,10 @@ lookup_fwd_tma_kernel(const __grid_constant__ LookupTmaParams p, const __grid_co
         slot = slot + 1 == kDepth ? 0 : slot + 1;
       }
       // both halves of the output tile are in shared memory: write it out as 128-byte rows
+      if (kNhwc) {
+        cur = nxt;
+        continue;
+      }
       named_bar_sync(1, kSamplerThreads);
       {
         const int xx = cur.x0 + lane;
@@ -396,22 +407,27 @@ bool tma_eligible(const raftcorr_level* levels, int L, int r) {
   return get_encode() != nullptr;
 }
 
-template <int R, int L, int kMode>
-int launch_tma(const LookupTmaParams& p, const LookupTmaMaps& maps, cudaStream_t stream) {
+template <int R, int L, int kMode, bool kNhwc>
+int launch_tma_k(const LookupTmaParams& p, const LookupTmaMaps& maps, cudaStream_t stream) {
   using C = Cfg<R, L>;
   int dev = 0;
   RC_CHECK_CUDA(cudaGetDevice(&dev));
   static std::atomic<int> sm_count[64];  // per device: 0 = kernel attribute not set yet
   int sms = (dev >= 0 && dev < 64) ? sm_count[dev].load(std::memory_order_acquire) : 0;
   if (sms == 0) {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(lookup_fwd_tma_kernel<R, L, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
+    RC_CHECK_CUDA(cudaFuncSetAttribute(lookup_fwd_tma_kernel<R, L, kMode, kNhwc>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem));
     RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (dev >= 0 && dev < 64) sm_count[dev].store(sms, std::memory_order_release);
   }
   const int grid = (int)(p.tiles < sms ? p.tiles : sms);
-  lookup_fwd_tma_kernel<R, L, kMode><<<grid, kThreadsTma, C::kSmem, stream>>>(p, maps);
+  lookup_fwd_tma_kernel<R, L, kMode, kNhwc><<<grid, kThreadsTma, C::kSmem, stream>>>(p, maps);
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+template <int R, int L, int kMode>
+int launch_tma(const LookupTmaParams& p, const LookupTmaMaps& maps, cudaStream_t stream) {
+  return p.nhwc ? launch_tma_k<R, L, kMode, true>(p, maps, stream) : launch_tma_k<R, L, kMode, false>(p, maps, stream);
 }
 
 }  // namespace
@@ -424,7 +440,7 @@ extern "C" int raftcorr_debug_wait_timeouts(unsigned long long* out8) {
 
 // returns 1 when the TMA path does not apply (caller uses the generic-stride kernel)
 int launch_lookup_fwd_tma(const raftcorr_level* levels, int L, const float* coords, float* out, int B,
-                          int H, int W, int r, int mode, cudaStream_t stream) {
+                          int H, int W, int r, int mode, int nhwc, cudaStream_t stream) {
   if (!tma_eligible(levels, L, r)) return 1;
   LookupTmaParams p;
   const long long BN = (long long)B * H * W;
@@ -462,6 +478,7 @@ int launch_lookup_fwd_tma(const raftcorr_level* levels, int L, const float* coor
   }
   p.coords = coords;
   p.out = out;
+  p.nhwc = nhwc;
   p.B = B;
   p.H = H;
   p.W = W;

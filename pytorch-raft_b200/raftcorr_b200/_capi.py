@@ -42,6 +42,8 @@ SIGNATURES = {
                                        [ctypes.POINTER(Level), ctypes.c_int, ctypes.c_void_p]),
     "raftcorr_lookup_fwd": (ctypes.c_int, [ctypes.POINTER(Level), ctypes.c_int, c_float_p, c_float_p] +
                             [ctypes.c_int] * 5 + [ctypes.c_void_p]),
+    "raftcorr_lookup_fwd_nhwc": (ctypes.c_int, [ctypes.POINTER(Level), ctypes.c_int, c_float_p, c_float_p] +
+                                 [ctypes.c_int] * 5 + [ctypes.c_void_p]),
     "raftcorr_lookup_bwd": (ctypes.c_int, [ctypes.POINTER(Level), ctypes.POINTER(Level), ctypes.c_int,
                                            c_float_p, c_float_p, c_float_p] + [ctypes.c_int] * 5 +
                             [ctypes.c_void_p]),

@@ -113,20 +113,26 @@ def build_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
     return pyr
 
 
-def lookup(pyr: Pyramid, coords: torch.Tensor, radius: int, coord_mode=None) -> torch.Tensor:
-    """core/corr.py:29-50: coords (B,2,H,W) -> (B, L*(2r+1)^2, H, W) fp32 contiguous."""
+def lookup(pyr: Pyramid, coords: torch.Tensor, radius: int, coord_mode=None, channels_last: bool = False) -> torch.Tensor:
+    """core/corr.py:29-50: coords (B,2,H,W) -> (B, L*(2r+1)^2, H, W) fp32, contiguous (NCHW) or, with
+    channels_last=True, the same logical tensor in torch.channels_last memory format."""
     _require_cuda_f32(coords, "coords")
     B, two, H, W = coords.shape
     if two != 2 or (B, H, W) != (pyr.B, pyr.H, pyr.W):
         raise RuntimeError(f"coords must be ({pyr.B},2,{pyr.H},{pyr.W}); got {tuple(coords.shape)}")
     coords = coords.contiguous()
     rd = 2 * radius + 1
-    out = torch.empty((B, pyr.num_levels * rd * rd, H, W), dtype=torch.float32, device=coords.device)
+    C = pyr.num_levels * rd * rd
+    if channels_last:
+        out = torch.empty((B, H, W, C), dtype=torch.float32, device=coords.device)
+        fn, name = _capi.lib().raftcorr_lookup_fwd_nhwc, "raftcorr_lookup_fwd_nhwc"
+    else:
+        out = torch.empty((B, C, H, W), dtype=torch.float32, device=coords.device)
+        fn, name = _capi.lib().raftcorr_lookup_fwd, "raftcorr_lookup_fwd"
     with _on_device(coords.device):
-        _capi.check(_capi.lib().raftcorr_lookup_fwd(pyr.desc, pyr.num_levels, coords.data_ptr(), out.data_ptr(),
-                                                    B, H, W, radius, resolve_coord_mode(coord_mode),
-                                                    _stream(coords)), "raftcorr_lookup_fwd")
-    return out
+        _capi.check(fn(pyr.desc, pyr.num_levels, coords.data_ptr(), out.data_ptr(), B, H, W, radius,
+                       resolve_coord_mode(coord_mode), _stream(coords)), name)
+    return out.permute(0, 3, 1, 2) if channels_last else out
 
 
 def lookup_backward(pyr: Optional[Pyramid], grad_pyr: Optional[Pyramid], coords: torch.Tensor,

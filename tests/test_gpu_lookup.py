@@ -163,3 +163,18 @@ def test_unpadded_contiguous_levels_are_accepted():
                                          torch.cuda.current_stream().cuda_stream)
     assert rc == 0, _capi.lib().raftcorr_last_error()
     assert np.array_equal(out.cpu().numpy(), oracle.lookup([l.numpy() for l in levels], c.numpy(), r))
+
+
+def test_channels_last_output_is_the_same_tensor():
+    """raftcorr_lookup_fwd_nhwc: same values as the NCHW entry point, laid out (B,H,W,C) — through both
+    the TMA kernel (4 levels, r=4/3) and the generic-stride kernel (other level counts / radii)."""
+    gen = torch.Generator().manual_seed(23)
+    for (B, H, W, L, r) in [(2, 55, 128, 4, 4), (1, 46, 62, 4, 4), (2, 17, 23, 4, 3), (1, 16, 95, 3, 2), (1, 9, 33, 2, 1)]:
+        pyr = ops.Pyramid(B, H, W, L, "cuda", zero=True)
+        for l in range(L):
+            pyr.storage[l][:, :, : pyr.desc[l].W].normal_()
+        c = coords_for("sigma4", B, H, W, gen).cuda()
+        a = ops.lookup(pyr, c, r)
+        b = ops.lookup(pyr, c, r, channels_last=True)
+        assert b.shape == a.shape and b.is_contiguous(memory_format=torch.channels_last)
+        assert torch.equal(a, b), (B, H, W, L, r)

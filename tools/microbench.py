@@ -68,6 +68,14 @@ def main():
     ms = timeit(g.replay, reps=10) / len(cs)
     byts = B * N * 2904
     print(f"lookup sigma4 (graph of 10, kernel only): {ms*1e3:.1f} us  {byts/ms/1e6:.0f} GB/s algorithmic ({byts/ms/1e6/PEAKS['hbm_gbs']:.2f} of measured HBM)")
+    g2 = torch.cuda.CUDAGraph()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g2, stream=side):
+            outs2 = [ops.lookup(pyr, c, 4, channels_last=True) for c in cs]
+    torch.cuda.current_stream().wait_stream(side)
+    ms = timeit(g2.replay, reps=10) / len(cs)
+    print(f"lookup sigma4 channels_last (graph of 10, kernel only): {ms*1e3:.1f} us  {byts/ms/1e6:.0f} GB/s algorithmic ({byts/ms/1e6/PEAKS['hbm_gbs']:.2f} of measured HBM)")
     import time
     torch.cuda.synchronize(); t0 = time.perf_counter()
     for _ in range(200): ops.lookup(pyr, cs[0], 4)
