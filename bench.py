@@ -156,6 +156,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=None, help="bf16 (default) | tf32 | fp32 for the volume build")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--channels-last", action="store_true",
+                    help="run the stock model in torch.channels_last and take the lookup in the same format")
     args = ap.parse_args()
     warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
 
@@ -197,9 +199,13 @@ def main():
     model = make_model(dev)
     host1, host2 = synthetic_frames(BATCH_PER_GPU, seed=100 + rank, pin=True)
     dev1, dev2 = host1.to(dev), host2.to(dev)
+    if args.channels_last:
+        model = model.to(memory_format=torch.channels_last)
+        dev1, dev2 = dev1.contiguous(memory_format=torch.channels_last), dev2.contiguous(memory_format=torch.channels_last)
     host_flow = torch.empty(BATCH_PER_GPU, 2, IMG_H, IMG_W).pin_memory()
     factory = lambda f1, f2, r: raftcorr_dropin.CorrBlock(f1, f2, num_levels=LEVELS, radius=r,  # noqa: E731
-                                                          precision=args.precision)
+                                                          precision=args.precision,
+                                                          channels_last=args.channels_last)
 
     lookup_events = []
 
@@ -299,7 +305,8 @@ def main():
         "dtype": "bf16" if args.precision in (None, "bf16") else args.precision,
         "data": "synthetic",
         "config": dict(base_config, l2="inputs exceed L2 (2.1 GB pyramid + 115 MB frames per step)",
-                       build_precision=args.precision or "bf16", encoders="stock PyTorch/cuDNN fp32"),
+                       build_precision=args.precision or "bf16", encoders="stock PyTorch/cuDNN fp32",
+                       memory_format="channels_last" if args.channels_last else "contiguous (NCHW, as the reference)"),
         "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": (2 + ITERS) * args.steps * n_gpus,   # pack + tcgen05 build + 12 lookups per step

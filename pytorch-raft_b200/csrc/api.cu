@@ -102,7 +102,7 @@ int raftcorr_pyramid_layout(int B, int H, int W, int num_levels, raftcorr_level*
 }
 
 int64_t raftcorr_build_workspace_bytes(int B, int D, int H, int W, int precision) {
-  if (precision == RAFTCORR_PREC_FP32 && D % 8 != 0) return 0;   // CUDA-core build, no workspace
+  if (D % 8 != 0) return 0;   // CUDA-core build (any precision request), no workspace
   return build_tc_workspace_bytes(B, D, H, W, precision);
 }
 
@@ -125,6 +125,10 @@ int raftcorr_build_pyramid(const float* fmap1, const float* fmap2, int B, int D,
       tc_ok = !(levels[l].pitch & 3) && !(levels[l].image_stride & 3) &&
               !(reinterpret_cast<uintptr_t>(levels[l].data) & 15);
     if (!tc_ok) return launch_build_fp32(fmap1, fmap2, B, D, H, W, num_levels, levels, (cudaStream_t)stream);
+  } else if (D % 8 != 0) {
+    // the tensor-core operand layout needs 16-byte rows of K; odd channel counts take the (more
+    // accurate) fp32 CUDA-core build instead of failing - the reference accepts any D
+    return launch_build_fp32(fmap1, fmap2, B, D, H, W, num_levels, levels, (cudaStream_t)stream);
   }
   return launch_build_tc(fmap1, fmap2, B, D, H, W, num_levels, levels, precision, workspace,
                          workspace_bytes, (cudaStream_t)stream);

@@ -91,6 +91,18 @@ def test_fp32_mode_full_size_is_fp32_accurate():
         assert err <= 1e-5, (D, err)
 
 
+def test_odd_channel_count_is_served_by_the_fp32_kernel():
+    """D % 8 != 0 cannot use the tensor-core operand layout; every precision request then runs the
+    fp32 CUDA-core build (the reference accepts any D)."""
+    gen = torch.Generator(device="cuda").manual_seed(6)
+    f1 = torch.randn(1, 12, 16, 20, device="cuda", generator=gen)
+    f2 = torch.randn(1, 12, 16, 20, device="cuda", generator=gen)
+    ref = torch.einsum("bdi,bdj->bij", f1.double().flatten(2), f2.double().flatten(2)) / (12 ** 0.5)
+    for precision in ("bf16", "tf32", "fp32"):
+        lv0 = ops.build_pyramid(f1, f2, 4, precision).views()[0].reshape(1, 320, 320)
+        assert (lv0.double() - ref).abs().max().item() <= 1e-5 * ref.abs().max().item(), precision
+
+
 def test_static_corr_and_idempotence():
     """CorrBlock.corr (corr.py:52-60) shape, and two builds of the same input agree bit for bit."""
     import corr
