@@ -38,6 +38,9 @@ for _p in (ROOT, PKG):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+# NCCL writes its banner / debug lines to stdout by default; stdout is reserved for the one JSON line
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
 import torch  # noqa: E402
 
 METRIC = "RAFT frame-pairs/s @440x1024 12 iters; corr lookup HBM GB/s vs peak"
@@ -156,6 +159,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=None, help="bf16 (default) | tf32 | fp32 for the volume build")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--cudnn-benchmark", action="store_true", help="let cuDNN autotune the stock convolutions")
     ap.add_argument("--channels-last", action="store_true",
                     help="run the stock model in torch.channels_last and take the lookup in the same format")
     args = ap.parse_args()
@@ -196,6 +200,7 @@ def main():
     dev = torch.device("cuda", local_rank if distributed else 0)
     torch.cuda.set_device(dev)
 
+    torch.backends.cudnn.benchmark = bool(args.cudnn_benchmark)
     model = make_model(dev)
     host1, host2 = synthetic_frames(BATCH_PER_GPU, seed=100 + rank, pin=True)
     dev1, dev2 = host1.to(dev), host2.to(dev)
