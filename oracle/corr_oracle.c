@@ -10,6 +10,12 @@
  * grid_sampler_2d, torch 2.11) is restated from its published semantics and pinned against the
  * reference itself run in the build container (oracle/make_golden.py -> tests/golden/).
  *
+ * Pin status: oracle_corr_volume / oracle_avg_pool2 / oracle_lookup are pinned against vectors the
+ * unmodified reference produced (tests/golden/, tests/test_oracle.py: pooling and lookup bit-exact,
+ * volume <= 1e-5).  oracle_alt_forward restates alt_cuda_corr's CUDA kernel, which cannot be executed
+ * without a GPU and may not be recompiled: for that function PARITY IS UNPINNED by execution; it is
+ * only cross-checked against the reference CorrBlock's output (pooling commutes with the dot product).
+ *
  * Build: gcc -O2 -ffp-contract=off -fopenmp -shared -fPIC (see oracle/Makefile).
  * -ffp-contract=off matters: the coordinate arithmetic must round after every operation
  * exactly as the separate ATen kernels do.
