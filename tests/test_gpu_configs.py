@@ -75,3 +75,28 @@ def test_cfg5_training_step_gradients():
     assert abs(loss.item() - rloss.item()) <= 1e-4 * abs(rloss.item()) + 1e-2
     for got, want in ((a.grad, ra.grad), (b_.grad, rb.grad)):
         assert torch.allclose(got, want, rtol=1e-3, atol=1e-4 * want.abs().max().item())
+
+
+def test_cfg4_volume_path_equals_on_the_fly_path_at_1088x1920():
+    """BASELINE.json configs[3] shape, one pair: the all-pairs volume at 136x240 is 5.7 GB per pair
+    (the reason the reference offers AlternateCorrBlock); on a 180 GB part both blocks fit, so the
+    largest configuration doubles as a cross-check of the two independent code paths: tensor-core
+    volume + TMA lookup versus fp32 on-the-fly dot products.  Same zero masks, values within the
+    bf16 bar."""
+    import corr
+    B, D, H, W = 1, 256, 136, 240
+    gen = torch.Generator(device="cuda").manual_seed(47)
+    f1 = torch.randn(B, D, H, W, device="cuda", generator=gen)
+    f2 = torch.randn(B, D, H, W, device="cuda", generator=gen)
+    low = 8 * torch.randn(B, 2, H // 8, W // 8, device="cuda", generator=gen)
+    c = _grid(B, H, W) + torch.nn.functional.interpolate(low, size=(H, W), mode="bilinear", align_corners=True)
+    with torch.no_grad():
+        vol = corr.CorrBlock(f1, f2)
+        assert [tuple(p.shape) for p in vol.corr_pyramid] == [(32640, 1, 136, 240), (32640, 1, 68, 120),
+                                                              (32640, 1, 34, 60), (32640, 1, 17, 30)]
+        a = vol(c)
+        b = corr.AlternateCorrBlock(f1, f2, precision="fp32")(c)
+        del vol
+    assert a.shape == b.shape == (1, 324, 136, 240)
+    assert torch.equal(a == 0, b == 0)
+    assert (a - b).abs().max().item() <= 1e-2 * b.abs().max().item()
