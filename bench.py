@@ -151,6 +151,66 @@ def run_cpu_reference(steps: int, warmup: int, sample_pairs: int = 1):
                       "oracle/torch_restatement.py (same ATen ops as core/corr.py) inside harness/raft_stock.py"}
 
 
+def measure_other_configs(dev, hbm_peak_gbs):
+    """Kernel-level numbers for the path's other BASELINE.json configurations (CUDA events, rank 0,
+    N=1 only; a few hundred ms): configs[3] on-the-fly path at 1088x1920, configs[4] training-step
+    correlation forward + backward.  Reported next to the headline, not part of it."""
+    import corr as raftcorr_dropin
+
+    def grid(B, H, W):
+        ys, xs = torch.meshgrid(torch.arange(H, device=dev), torch.arange(W, device=dev), indexing="ij")
+        return torch.stack([xs, ys]).float()[None].repeat(B, 1, 1, 1)
+
+    def timed(fn, reps, warm=2):
+        for _ in range(warm):
+            fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    out = {}
+    gen = torch.Generator(device=dev).manual_seed(7)
+    # configs[3]: AlternateCorrBlock, 136x240 fmaps, D=256, batch 4, smooth flow (SURVEY.md 8d-iii)
+    B, D, H, W = 4, 256, 136, 240
+    f1 = torch.randn(B, D, H, W, device=dev, generator=gen)
+    f2 = torch.randn(B, D, H, W, device=dev, generator=gen)
+    low = 8 * torch.randn(B, 2, H // 8, W // 8, device=dev, generator=gen)
+    c = grid(B, H, W) + torch.nn.functional.interpolate(low, size=(H, W), mode="bilinear", align_corners=True)
+    with torch.no_grad():
+        blk = raftcorr_dropin.AlternateCorrBlock(f1, f2)
+        ms = timed(lambda: blk(c), reps=10)
+    N = H * W
+    T = sum((H >> l) * (W >> l) for l in range(4))
+    compulsory = B * (N * D * 4 + T * D * 4 + 8 * N + 1296 * N)          # SURVEY.md 8(d): 120.4 MB per pair
+    useful_flops = B * N * 4 * 100 * 2 * D
+    out["alt_cfg4"] = {"workload": "AlternateCorrBlock 1088x1920 (136x240 fmaps), batch 4, D=256, smooth flow",
+                       "ms_per_iter": ms, "compulsory_gb_s": compulsory / ms / 1e6,
+                       "frac_hbm_at_compulsory_bytes": compulsory / ms / 1e6 / hbm_peak_gbs,
+                       "useful_tflops": useful_flops / ms / 1e9, "binding": "sampler issue slots (tensor pipe 27 % active)"}
+    del f1, f2, blk
+    # configs[4]: CorrBlock forward + backward of 12 lookups at 368x496, batch 12
+    B, D, H, W = 12, 256, 46, 62
+    f1 = torch.randn(B, D, H, W, device=dev, generator=gen, requires_grad=True)
+    f2 = torch.randn(B, D, H, W, device=dev, generator=gen, requires_grad=True)
+    c = grid(B, H, W) + 4 * torch.randn(B, 2, H, W, device=dev, generator=gen)
+
+    def train_step():
+        blk = raftcorr_dropin.CorrBlock(f1, f2)
+        loss = 0
+        for _ in range(ITERS):
+            loss = loss + blk(c).sum()
+        loss.backward()
+        f1.grad = f2.grad = None
+
+    out["train_cfg5"] = {"workload": "CorrBlock build + 12 lookups, forward and backward, 368x496 (46x62 fmaps), batch 12",
+                         "ms_per_step": timed(train_step, reps=3, warm=1)}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -324,6 +384,8 @@ def main():
                     "corr_path_share_of_step": (build_ms + ITERS * lookup_avg_ms) / (ms_total / args.steps)},
         "clocks": clocks,
     }
+    if n_gpus == 1:
+        line["other_configs"] = measure_other_configs(dev, peak)
     if not args.skip_cpu_baseline and n_gpus == 1:
         ref = run_cpu_reference(steps=1, warmup=1)
         line["cpu_baseline"] = {"value": ref["value"], "unit": UNIT, "cores": ref["cores"], "kind": ref["kind"],
