@@ -77,14 +77,14 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
   extern __shared__ __align__(1024) unsigned char smem[];
   const uint32_t smem_base = smem_u32(smem);
   float* S_s = reinterpret_cast<float*>(smem + kOffS);
-  int* ubox = reinterpret_cast<int*>(smem + kOffMisc);          // x0, y0, x1, y1 of the union
-  const uint32_t bars = smem_base + kOffMisc + 32;
+  int* ubox = reinterpret_cast<int*>(smem + kOffMisc);          // per level: x0, y0, x1, y1 of the union
+  const uint32_t bars = smem_base + kOffMisc + 64;
   auto full_bar = [&](int s) { return bars + 8 * s; };
   auto empty_bar = [&](int s) { return bars + 8 * (kBStages + s); };
   auto tfull_bar = [&](int a) { return bars + 8 * (2 * kBStages + a); };
   auto tempty_bar = [&](int a) { return bars + 8 * (2 * kBStages + 2 + a); };
   const uint32_t afull_bar = bars + 8 * (2 * kBStages + 4);
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffMisc + 32 + 8 * (2 * kBStages + 5));
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffMisc + 64 + 8 * (2 * kBStages + 5));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -140,15 +140,34 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
   uint32_t it = 0;      // B-stage counter (producer and MMA count the same sequence)
   uint32_t chunk_no = 0;  // accumulator-stage counter (MMA and samplers)
 
+  // Union of the tile's windows at every level, computed once up front so that the TMA / MMA
+  // pipeline can run across level boundaries without a CTA barrier per level.
+  if (threadIdx.x < 4 * RAFTCORR_MAX_LEVELS) ubox[threadIdx.x] = (threadIdx.x & 2) ? -(1 << 30) : (1 << 30);
+  __syncthreads();
+  if (valid && warp < 6) {   // one sampler warp per TMEM lane quarter (x group 0) reports its queries
+    for (int l = 0; l < p.L; ++l) {
+      const AltTcLevel& lv = p.lv[l];
+      const float lx = __fmul_rn(cx, lv.inv_pow2), ly = __fmul_rn(cy, lv.inv_pow2);
+      const int xa = max(make_tap_fast(lx, (float)(-R), lv.sm1x, lv.invx, lv.halfx, kMode).i0, 0);
+      const int xb = min(make_tap_fast(lx, (float)R, lv.sm1x, lv.invx, lv.halfx, kMode).i0 + 1, lv.W - 1);
+      const int ya = max(make_tap_fast(ly, (float)(-R), lv.sm1y, lv.invy, lv.halfy, kMode).i0, 0);
+      const int yb = min(make_tap_fast(ly, (float)R, lv.sm1y, lv.invy, lv.halfy, kMode).i0 + 1, lv.H - 1);
+      if (xa <= xb && ya <= yb) {
+        atomicMin(&ubox[4 * l + 0], xa);
+        atomicMin(&ubox[4 * l + 1], ya);
+        atomicMax(&ubox[4 * l + 2], xb);
+        atomicMax(&ubox[4 * l + 3], yb);
+      }
+    }
+  }
+  __syncthreads();
+
   for (int l = 0; l < p.L; ++l) {
     const AltTcLevel& lv = p.lv[l];
-    if (threadIdx.x == 0) {
-      ubox[0] = 1 << 30;
-      ubox[1] = 1 << 30;
-      ubox[2] = -(1 << 30);
-      ubox[3] = -(1 << 30);
-    }
-    __syncthreads();
+    const int ux0 = ubox[4 * l + 0], uy0 = ubox[4 * l + 1], ux1 = ubox[4 * l + 2], uy1 = ubox[4 * l + 3];
+    const int ncx = ux1 >= ux0 ? (ux1 - ux0 + kChunkW) / kChunkW : 0;
+    const int ncy = uy1 >= uy0 ? (uy1 - uy0 + kChunkH) / kChunkH : 0;
+    const int n_chunks = ncx * ncy;
 
     // ---- tap tables of this thread's query at this level (registers) ----
     constexpr int kXPer = (rd + kXGroups - 1) / kXGroups;   // x taps per warp group
@@ -177,12 +196,6 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
       my_y_lo = max(y0[0], 0);
       my_y_hi = min(y0[rd - 1] + 1, lv.H - 1);
       if (q_x_lo <= q_x_hi && my_y_lo <= my_y_hi) {
-        if (xg == 0) {   // one warp per lane quarter reports the query's window
-          atomicMin(&ubox[0], q_x_lo);
-          atomicMin(&ubox[1], my_y_lo);
-          atomicMax(&ubox[2], q_x_hi);
-          atomicMax(&ubox[3], my_y_hi);
-        }
         // columns this warp's own taps touch
         my_x_lo = max(x0[0], 0);
         my_x_hi = min(x0[kXPer - 1] + 1, lv.W - 1);
@@ -202,12 +215,6 @@ alt_tc_kernel(const __grid_constant__ AltTcParams p, const __grid_constant__ Alt
         wx[t] = 0.0f;
       }
     }
-    __syncthreads();
-    const int ux0 = ubox[0], uy0 = ubox[1], ux1 = ubox[2], uy1 = ubox[3];
-    const int ncx = ux1 >= ux0 ? (ux1 - ux0 + kChunkW) / kChunkW : 0;
-    const int ncy = uy1 >= uy0 ? (uy1 - uy0 + kChunkH) / kChunkH : 0;
-    const int n_chunks = ncx * ncy;
-
     if (warp == 0) {
       if (lane == 0) {
         for (int c = 0; c < n_chunks; ++c) {
