@@ -151,6 +151,22 @@ int raftcorr_alt_bwd(const float* fmap1, const float* fmap2, const float* coords
                      float* coords_grad, int B, int H1, int W1, int H2, int W2, int C, int radius,
                      int coord_mode, float scale, void* stream);
 
+/* ---- (4) the step after the path: convex 8x upsampling, replaces RAFT.upsample_flow
+ *      (core/raft.py:72-83: view + softmax + unfold + mul + sum + permute + reshape) in one pass.
+ *      flow: (B,2,H,W) fp32; mask: (B,576,H,W) fp32, channel = k*64 + dy*8 + dx with k = 3*ky+kx the 3x3
+ *      neighbour (zero padded) and (dy,dx) the sub-pixel; up: (B,2,8H,8W) fp32.
+ *      up[b,c,8y+dy,8x+dx] = sum_k softmax_k(mask[b,k,dy,dx,y,x]) * 8*flow[b,c,y+ky-1,x+kx-1]. */
+int raftcorr_upsample_flow_fwd(const float* flow, const float* mask, float* up, int B, int H, int W,
+                               void* stream);
+/* Backward of the above (the training loss reads every iteration's upsampled flow, train.py:47-72).
+ * grad_flow (B,2,H,W) is overwritten (zeroed on `stream`, then accumulated with atomics); grad_mask
+ * (B,576,H,W) is overwritten; either may be NULL. */
+int raftcorr_upsample_flow_bwd(const float* flow, const float* mask, const float* grad_up, float* grad_flow,
+                               float* grad_mask, int B, int H, int W, void* stream);
+/* 8 * bilinear x8 interpolation with align_corners=True: replaces upflow8, core/utils/utils.py:80-82
+ * (the small model's upsampling, raft.py:134-135).  flow (B,2,H,W) -> up (B,2,8H,8W). */
+int raftcorr_upflow8(const float* flow, float* up, int B, int H, int W, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

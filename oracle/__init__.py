@@ -152,3 +152,22 @@ def alt_corr_block(fmap1, fmap2, coords, num_levels: int = 4, radius: int = 4,
         f2_l = avg_pool2(f2_l)
     corr = np.stack(outs, axis=1).reshape(B, -1, H, W)
     return corr / np.sqrt(np.float32(D))
+
+
+def upsample_flow(flow, mask) -> np.ndarray:
+    """RAFT.upsample_flow (core/raft.py:72-83).  flow (B,2,H,W), mask (B,576,H,W) -> (B,2,8H,8W)."""
+    f, m = _f32(flow), _f32(mask)
+    B, _, H, W = f.shape
+    assert m.shape == (B, 576, H, W)
+    up = np.empty((B, 2, 8 * H, 8 * W), dtype=np.float32)
+    lib().oracle_upsample_flow(_fp(f), _fp(m), _fp(up), B, H, W)
+    return up
+
+
+def upflow8(flow) -> np.ndarray:
+    """upflow8 (core/utils/utils.py:80-82).  flow (B,2,H,W) -> (B,2,8H,8W)."""
+    f = _f32(flow)
+    B, _, H, W = f.shape
+    up = np.empty((B, 2, 8 * H, 8 * W), dtype=np.float32)
+    lib().oracle_upflow8(_fp(f), _fp(up), B, H, W)
+    return up

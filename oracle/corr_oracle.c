@@ -244,3 +244,64 @@ void oracle_alt_forward(const float* fmap1, const float* fmap2, const float* coo
     }
   }
 }
+
+/* ---- the step after the path: convex 8x upsampling (core/raft.py:72-83) --------------------
+ * mask (B,576,H,W) viewed (B,1,9,8,8,H,W) and soft-maxed over the 9 (raft.py:75-76); 8*flow
+ * unfolded 3x3 with zero padding (raft.py:78-79); weighted sum over the 9 (raft.py:81); the
+ * permute/reshape of raft.py:82-83 puts sub-pixel (dy,dx) of coarse (y,x) at (8y+dy, 8x+dx). */
+void oracle_upsample_flow(const float* flow, const float* mask, float* up, int B, int H, int W) {
+  const int64_t cs = (int64_t)H * W;
+#pragma omp parallel for schedule(static)
+  for (int64_t row = 0; row < (int64_t)B * H; ++row) {
+    const int b = (int)(row / H), y = (int)(row % H);
+    for (int x = 0; x < W; ++x)
+      for (int dy = 0; dy < 8; ++dy)
+        for (int dx = 0; dx < 8; ++dx) {
+          float v[9], mx = -INFINITY, sum = 0.0f;
+          for (int k = 0; k < 9; ++k) {
+            v[k] = mask[((int64_t)b * 576 + k * 64 + dy * 8 + dx) * cs + (int64_t)y * W + x];
+            if (v[k] > mx) mx = v[k];
+          }
+          for (int k = 0; k < 9; ++k) {
+            v[k] = expf(v[k] - mx);
+            sum += v[k];
+          }
+          for (int c = 0; c < 2; ++c) {
+            float acc = 0.0f;
+            for (int k = 0; k < 9; ++k) {
+              const int yy = y + k / 3 - 1, xx = x + k % 3 - 1;
+              const float f = (yy < 0 || yy >= H || xx < 0 || xx >= W)
+                                  ? 0.0f
+                                  : 8.0f * flow[((int64_t)b * 2 + c) * cs + (int64_t)yy * W + xx];
+              acc += (v[k] / sum) * f;
+            }
+            up[(((int64_t)b * 2 + c) * 8 * H + 8 * y + dy) * 8 * W + 8 * x + dx] = acc;
+          }
+        }
+  }
+}
+
+/* 8 * F.interpolate(flow, 8x, bilinear, align_corners=True) (core/utils/utils.py:80-82); source index
+ * = dst * (in-1)/(out-1) as ATen's area_pixel_compute_source_index does for align_corners. */
+void oracle_upflow8(const float* flow, float* up, int B, int H, int W) {
+  const int H8 = 8 * H, W8 = 8 * W;
+  const float sy = H8 > 1 ? (float)(H - 1) / (float)(H8 - 1) : 0.0f;
+  const float sx = W8 > 1 ? (float)(W - 1) / (float)(W8 - 1) : 0.0f;
+#pragma omp parallel for schedule(static)
+  for (int64_t row = 0; row < (int64_t)B * 2 * H8; ++row) {
+    const int64_t img = row / H8;
+    const int oy = (int)(row % H8);
+    const float fy = sy * (float)oy;
+    const int y0 = (int)fy, y1 = y0 + (y0 < H - 1 ? 1 : 0);
+    const float ly = fy - (float)y0, hy = 1.0f - ly;
+    const float* src = flow + img * (int64_t)H * W;
+    for (int ox = 0; ox < W8; ++ox) {
+      const float fx = sx * (float)ox;
+      const int x0 = (int)fx, x1 = x0 + (x0 < W - 1 ? 1 : 0);
+      const float lx = fx - (float)x0, hx = 1.0f - lx;
+      const float v = hy * (hx * src[y0 * W + x0] + lx * src[y0 * W + x1]) +
+                      ly * (hx * src[y1 * W + x0] + lx * src[y1 * W + x1]);
+      up[row * W8 + ox] = 8.0f * v;
+    }
+  }
+}

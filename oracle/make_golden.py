@@ -11,6 +11,7 @@ Cases
   tiny      B=1 D=8   16x18  r=4 L=4  inputs + full pyramid + outputs for 4 coord distributions,
                                       plus autograd grads (d fmap1, d fmap2, d coords)
   odd_r3    B=2 D=8   17x23  r=3 L=4  inputs + levels 1..3 + outputs (odd sizes, sqrt(8) scale, r=3)
+  upsample  N=2 7x11: RAFT.upsample_flow (raft.py:72-83) output and autograd grads, upflow8 output
   cfg1      B=1 D=256 46x62  r=4 L=4  BASELINE.json configs[0]; inputs regenerated from the seed
                                       (torch CPU generator), outputs stored as strided samples +
                                       float64 checksums + zero counts
@@ -115,6 +116,21 @@ def main() -> None:
         rec[f"out_{kind}_sample"] = o[:, :, ::5, ::7]
         rec[f"out_{kind}_zero_rows"] = (o == 0).sum(axis=(0, 2, 3)).astype(np.int32)
     np.savez(os.path.join(OUT, "corr_cfg1.npz"), **rec)
+    # ---- the step after the path: RAFT.upsample_flow / upflow8 (raft.py:72-83, utils.py:80-82) ----
+    import argparse
+    from raft import RAFT  # the reference, unmodified
+    from utils.utils import upflow8
+    model = RAFT(argparse.Namespace(small=False, mixed_precision=False, alternate_corr=False))
+    gen = torch.Generator().manual_seed(1237)
+    N, H, W = 2, 7, 11
+    flow = (4 * torch.randn(N, 2, H, W, generator=gen)).requires_grad_(True)
+    mask = (3 * torch.randn(N, 576, H, W, generator=gen)).requires_grad_(True)
+    up = model.upsample_flow(flow, mask)
+    gup = torch.randn(up.shape, generator=gen)
+    up.backward(gup)
+    np.savez(os.path.join(OUT, "upsample_tiny.npz"), flow=flow.detach().numpy(), mask=mask.detach().numpy(),
+             up=up.detach().numpy(), grad_up=gup.numpy(), grad_flow=flow.grad.numpy(),
+             grad_mask=mask.grad.numpy(), up8=upflow8(flow.detach()).numpy())
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))
 

@@ -112,3 +112,19 @@ def alt_corr_block_math(fmap1, fmap2, coords, num_levels: int = 4, radius: int =
         f2 = F.avg_pool2d(f2, 2, stride=2)
     corr = torch.cat(outs, dim=-1).permute(0, 3, 1, 2).contiguous()
     return corr / math.sqrt(D)
+
+
+def upsample_flow(flow: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
+    """RAFT.upsample_flow restated op for op (core/raft.py:72-83): the op sequence the reference runs after
+    every iteration; used to time "what the reference does" and as the autograd oracle for the backward."""
+    N, _, H, W = flow.shape
+    weights = torch.softmax(mask.view(N, 1, 9, 8, 8, H, W), dim=2)                      # raft.py:75-76
+    patches = F.unfold(8 * flow, [3, 3], padding=1).view(N, 2, 9, 1, 1, H, W)           # raft.py:78-79
+    fine = torch.sum(weights * patches, dim=2)                                          # raft.py:81
+    return fine.permute(0, 1, 4, 2, 5, 3).reshape(N, 2, 8 * H, 8 * W)                   # raft.py:82-83
+
+
+def upflow8(flow: torch.Tensor) -> torch.Tensor:
+    """core/utils/utils.py:80-82."""
+    size = (8 * flow.shape[2], 8 * flow.shape[3])
+    return 8 * F.interpolate(flow, size=size, mode="bilinear", align_corners=True)

@@ -50,6 +50,10 @@ int launch_alt_fwd(const float* f1, const float* f2, const float* coords, float*
                    int W1, int H2, int W2, int C, int r, int mode, float scale, cudaStream_t stream);
 int launch_alt_tc(const void* f1_bf16, const void* const* f2_bf16, const float* coords, float* out, int B,
                   int H1, int W1, int C, int L, int r, int mode, float scale, cudaStream_t stream);
+int launch_upsample_fwd(const float* flow, const float* mask, float* up, int B, int H, int W, cudaStream_t stream);
+int launch_upsample_bwd(const float* flow, const float* mask, const float* gup, float* gflow, float* gmask, int B,
+                        int H, int W, cudaStream_t stream);
+int launch_upflow8(const float* flow, float* up, int B, int H, int W, cudaStream_t stream);
 int launch_alt_bwd(const float* f1, const float* f2, const float* coords, const float* gcorr,
                    float* g1, float* g2, float* gcoords, int B, int H1, int W1, int H2, int W2, int C,
                    int r, int mode, float scale, cudaStream_t stream);
@@ -237,6 +241,32 @@ int raftcorr_alt_bwd(const float* fmap1, const float* fmap2, const float* coords
   RC_REQUIRE(valid_mode(coord_mode), "alt_bwd: coord_mode=%d", coord_mode);
   return launch_alt_bwd(fmap1, fmap2, coords, corr_grad, fmap1_grad, fmap2_grad, coords_grad, B, H1,
                         W1, H2, W2, C, radius, coord_mode, scale, (cudaStream_t)stream);
+}
+
+int raftcorr_upsample_flow_fwd(const float* flow, const float* mask, float* up, int B, int H, int W,
+                               void* stream) {
+  RC_REQUIRE(flow && mask && up, "upsample_flow_fwd: NULL pointer");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "upsample_flow_fwd: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(B <= 65535 && H <= 65535, "upsample_flow_fwd: B and H must fit a CUDA grid dimension");
+  RC_REQUIRE(!(reinterpret_cast<uintptr_t>(up) & 15), "upsample_flow_fwd: up must be 16-byte aligned");
+  return launch_upsample_fwd(flow, mask, up, B, H, W, (cudaStream_t)stream);
+}
+
+int raftcorr_upsample_flow_bwd(const float* flow, const float* mask, const float* grad_up, float* grad_flow,
+                               float* grad_mask, int B, int H, int W, void* stream) {
+  RC_REQUIRE(flow && mask && grad_up, "upsample_flow_bwd: NULL pointer");
+  RC_REQUIRE(grad_flow || grad_mask, "upsample_flow_bwd: nothing to compute");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "upsample_flow_bwd: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(B <= 65535 && H <= 65535, "upsample_flow_bwd: B and H must fit a CUDA grid dimension");
+  RC_REQUIRE(!(reinterpret_cast<uintptr_t>(grad_up) & 15), "upsample_flow_bwd: grad_up must be 16-byte aligned");
+  return launch_upsample_bwd(flow, mask, grad_up, grad_flow, grad_mask, B, H, W, (cudaStream_t)stream);
+}
+
+int raftcorr_upflow8(const float* flow, float* up, int B, int H, int W, void* stream) {
+  RC_REQUIRE(flow && up, "upflow8: NULL pointer");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "upflow8: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(!(reinterpret_cast<uintptr_t>(up) & 15), "upflow8: up must be 16-byte aligned");
+  return launch_upflow8(flow, up, B, H, W, (cudaStream_t)stream);
 }
 
 }  // extern "C"

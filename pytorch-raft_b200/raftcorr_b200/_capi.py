@@ -57,6 +57,9 @@ SIGNATURES = {
                                [ctypes.c_int] * 7 + [ctypes.c_float, ctypes.c_void_p]),
     "raftcorr_alt_bwd": (ctypes.c_int, [c_float_p] * 7 + [ctypes.c_int] * 8 + [ctypes.c_float,
                                                                               ctypes.c_void_p]),
+    "raftcorr_upsample_flow_fwd": (ctypes.c_int, [c_float_p] * 3 + [ctypes.c_int] * 3 + [ctypes.c_void_p]),
+    "raftcorr_upsample_flow_bwd": (ctypes.c_int, [c_float_p] * 5 + [ctypes.c_int] * 3 + [ctypes.c_void_p]),
+    "raftcorr_upflow8": (ctypes.c_int, [c_float_p] * 2 + [ctypes.c_int] * 3 + [ctypes.c_void_p]),
 }
 
 _lib = None

@@ -294,3 +294,68 @@ class AltFn(torch.autograd.Function):
         g1, g2, gc = alt_backward(fmap1, fmap2, coords, grad.contiguous(), ctx.radius, ctx.coord_mode,
                                   ctx.scale, want_coords=ctx.needs_input_grad[2])
         return g1, g2, gc, None, None, None
+
+
+# ---- the step after the path: flow upsampling ------------------------------------
+
+def _check_flow_mask(flow: torch.Tensor, mask: Optional[torch.Tensor]):
+    _require_cuda_f32(flow, "flow")
+    if flow.dim() != 4 or flow.shape[1] != 2:
+        raise RuntimeError(f"flow must be (B,2,H,W), got {tuple(flow.shape)}")
+    if mask is not None:
+        _require_cuda_f32(mask, "mask")
+        B, _, H, W = flow.shape
+        if tuple(mask.shape) != (B, 576, H, W):
+            raise RuntimeError(f"mask must be (B,576,H,W) = {(B, 576, H, W)}, got {tuple(mask.shape)}")
+        if mask.device != flow.device:
+            raise RuntimeError("flow and mask must be on the same device")
+
+
+def upsample_flow_forward(flow: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
+    _check_flow_mask(flow, mask)
+    flow, mask = flow.contiguous(), mask.contiguous()
+    B, _, H, W = flow.shape
+    up = torch.empty((B, 2, 8 * H, 8 * W), dtype=torch.float32, device=flow.device)
+    with _on_device(flow.device):
+        _capi.check(_capi.lib().raftcorr_upsample_flow_fwd(flow.data_ptr(), mask.data_ptr(), up.data_ptr(), B, H, W,
+                                                           _stream(flow)), "raftcorr_upsample_flow_fwd")
+    return up
+
+
+def upsample_flow_backward(flow: torch.Tensor, mask: torch.Tensor, grad_up: torch.Tensor, want_flow: bool = True,
+                           want_mask: bool = True):
+    _check_flow_mask(flow, mask)
+    flow, mask, grad_up = flow.contiguous(), mask.contiguous(), grad_up.contiguous()
+    B, _, H, W = flow.shape
+    gflow = torch.empty_like(flow) if want_flow else None
+    gmask = torch.empty_like(mask) if want_mask else None
+    with _on_device(flow.device):
+        _capi.check(_capi.lib().raftcorr_upsample_flow_bwd(
+            flow.data_ptr(), mask.data_ptr(), grad_up.data_ptr(), gflow.data_ptr() if want_flow else None,
+            gmask.data_ptr() if want_mask else None, B, H, W, _stream(flow)), "raftcorr_upsample_flow_bwd")
+    return gflow, gmask
+
+
+def upflow8_forward(flow: torch.Tensor) -> torch.Tensor:
+    _check_flow_mask(flow, None)
+    flow = flow.contiguous()
+    B, _, H, W = flow.shape
+    up = torch.empty((B, 2, 8 * H, 8 * W), dtype=torch.float32, device=flow.device)
+    with _on_device(flow.device):
+        _capi.check(_capi.lib().raftcorr_upflow8(flow.data_ptr(), up.data_ptr(), B, H, W, _stream(flow)),
+                    "raftcorr_upflow8")
+    return up
+
+
+class UpsampleFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, flow, mask):
+        ctx.save_for_backward(flow, mask)
+        return upsample_flow_forward(flow, mask)
+
+    @staticmethod
+    def backward(ctx, grad_up):
+        flow, mask = ctx.saved_tensors
+        if not (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]):
+            return None, None
+        return upsample_flow_backward(flow, mask, grad_up, ctx.needs_input_grad[0], ctx.needs_input_grad[1])

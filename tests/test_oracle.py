@@ -145,3 +145,21 @@ def test_alt_path_matches_corrblock_math(golden):
     t = tr.alt_corr_block_math(torch.from_numpy(g["fmap1"]), torch.from_numpy(g["fmap2"]),
                                torch.from_numpy(g["coords_sigma4"]), 4, 4).numpy()
     assert np.abs(t - out).max() <= 2e-5 * np.abs(ref).max()
+
+
+def test_upsample_flow_restatements_match_reference(golden):
+    """RAFT.upsample_flow / upflow8 (raft.py:72-83, utils.py:80-82): C loops and torch restatement vs the
+    reference's own outputs and autograd grads."""
+    from helpers import rel_max
+    g = golden("upsample_tiny")
+    up = oracle.upsample_flow(g["flow"], g["mask"])
+    assert rel_max(up, g["up"]) <= 1e-6
+    assert rel_max(oracle.upflow8(g["flow"]), g["up8"]) <= 1e-6
+    flow = torch.from_numpy(g["flow"]).requires_grad_(True)
+    mask = torch.from_numpy(g["mask"]).requires_grad_(True)
+    out = tr.upsample_flow(flow, mask)
+    assert np.array_equal(out.detach().numpy(), g["up"])
+    out.backward(torch.from_numpy(g["grad_up"]))
+    assert np.array_equal(flow.grad.numpy(), g["grad_flow"])
+    assert np.array_equal(mask.grad.numpy(), g["grad_mask"])
+    assert np.array_equal(tr.upflow8(flow.detach()).numpy(), g["up8"])
