@@ -219,6 +219,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=None, help="bf16 (default) | tf32 | fp32 for the volume build")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--stock-upsample", action="store_true",
+                    help="run RAFT.upsample_flow as the reference's torch op sequence instead of this library's kernel")
     ap.add_argument("--cudnn-benchmark", action="store_true", help="let cuDNN autotune the stock convolutions")
     ap.add_argument("--channels-last", action="store_true",
                     help="run the stock model in torch.channels_last and take the lookup in the same format")
@@ -287,15 +289,20 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    upsampler = None
+    if not args.stock_upsample:
+        import upsample as raftcorr_upsample
+        upsampler = raftcorr_upsample.upsample_flow
+
     def step_resident(hook=None):
         with torch.no_grad():
-            return model(dev1, dev2, factory, iters=ITERS, lookup_hook=hook)[1]
+            return model(dev1, dev2, factory, iters=ITERS, lookup_hook=hook, upsampler=upsampler)[1]
 
     def step_e2e():
         with torch.no_grad():
             a = host1.to(dev, non_blocking=True)
             b = host2.to(dev, non_blocking=True)
-            flow = model(a, b, factory, iters=ITERS)[1]
+            flow = model(a, b, factory, iters=ITERS, upsampler=upsampler)[1]
             host_flow.copy_(flow, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return host_flow
@@ -371,10 +378,13 @@ def main():
         "data": "synthetic",
         "config": dict(base_config, l2="inputs exceed L2 (2.1 GB pyramid + 115 MB frames per step)",
                        build_precision=args.precision or "bf16", encoders="stock PyTorch/cuDNN fp32",
+                       upsample="stock torch ops (raft.py:72-83)" if args.stock_upsample else
+                       "raftcorr_upsample_flow_fwd, every iteration like the reference",
                        memory_format="channels_last" if args.channels_last else "contiguous (NCHW, as the reference)"),
         "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": (2 + ITERS) * args.steps * n_gpus,   # pack + tcgen05 build + 12 lookups per step
+        # pack + tcgen05 build + 12 lookups (+ 12 convex upsamplings) per step
+        "gpu_launches": (2 + ITERS * (1 if args.stock_upsample else 2)) * args.steps * n_gpus,
         "roofline": {"kernel": "lookup_fwd_tma_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic_per_launch(),
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": queries * LOOKUP_BYTES_PER_QUERY,

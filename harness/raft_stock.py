@@ -168,8 +168,12 @@ class StockRAFT(nn.Module):
         net, inp = torch.split(self.cnet(image1), [self.hidden, self.context], dim=1)
         return fmap1.float(), fmap2.float(), torch.tanh(net), torch.relu(inp)
 
-    def forward(self, image1, image2, corr_factory, iters: int = 12, flow_init=None, lookup_hook=None):
-        """Returns (flow at 1/8 resolution, upsampled flow) like raft.py's test_mode."""
+    def forward(self, image1, image2, corr_factory, iters: int = 12, flow_init=None, lookup_hook=None,
+                upsampler=None):
+        """Returns (flow at 1/8 resolution, upsampled flow) like raft.py's test_mode.  ``upsampler(flow, mask)``
+        replaces raft.py:72-83 (default: the stock-torch op sequence); like the reference it runs after
+        every iteration (raft.py:134-139)."""
+        upsampler = upsampler or convex_upsample
         fmap1, fmap2, net, inp = self.features(image1, image2)
         corr_fn = corr_factory(fmap1, fmap2, self.radius)
         B, _, H, W = fmap1.shape
@@ -181,5 +185,5 @@ class StockRAFT(nn.Module):
             corr = corr_fn(coords1) if lookup_hook is None else lookup_hook(corr_fn, coords1)
             net, up_mask, delta = self.update_block(net, inp, corr, coords1 - coords0)
             coords1 = coords1 + delta
-            flow_up = convex_upsample(coords1 - coords0, up_mask)
+            flow_up = upsampler(coords1 - coords0, up_mask)
         return coords1 - coords0, flow_up

@@ -36,6 +36,13 @@ def test_twelve_iteration_flow_epe(shape):
         assert up.shape == up_ref.shape == (B, 2, Hi, Wi)
         epe = (up - up_ref).pow(2).sum(1).sqrt().mean().item()
         assert epe <= bound, (precision, epe, mag)
+    # ... and with the library's convex-upsampling kernel in place of raft.py:72-83 as well
+    import upsample
+    with torch.no_grad():
+        lo, up = model(im1, im2, lambda a, b, r: corr.CorrBlock(a, b, radius=r), iters=12,
+                       upsampler=upsample.upsample_flow)
+    epe = (up - up_ref).pow(2).sum(1).sqrt().mean().item()
+    assert epe <= 0.01, ("upsample", epe)
     # the memory-lean block computes the same flow
     lo, up = _flows(model, im1[:1], im2[:1], lambda a, b, r: corr.AlternateCorrBlock(a, b, radius=r))
     epe = (up - up_ref[:1]).pow(2).sum(1).sqrt().mean().item()
