@@ -96,95 +96,181 @@ __global__ void __launch_bounds__(kThreads) upsample_fwd_kernel(const float* __r
   }
 }
 
-// ---- TMA-fed forward (W % 4 == 0) ---------------------------------------------------------------------
-// The mask is viewed as a 4-D tensor {W, H, 64 sub-pixels, 9*B taps}; one box {32 x, 1 y, 8 dx, 9 k} =
-// 9216 B is everything one warp needs for one dy of one 32-pixel row segment.  Each warp of a persistent
-// CTA owns a two-slot ring of such boxes and is its own producer: it issues the box of its next work item,
-// then computes the current one, so ~12 x 9 KB are always in flight per SM and the loads cost one
-// instruction each.  A lane ends up holding the 8 dx of one x for both flow channels = two 32-byte runs
-// of the output, which leave as 256-bit stores; nothing is staged for the output.
-constexpr int kUpWarps = 12;
-constexpr int kBoxBytes = 9 * 8 * kTileX * 4;  // 9216
-constexpr int kUpSmem = kUpWarps * 2 * kBoxBytes + kUpWarps * 2 * 8;
+// ---- TMA-fed kernels (H*W % 4 == 0) -----------------------------------------------------------------
+// The mask is viewed as a 3-D tensor {H*W pixels, 64 sub-pixels, 9*B taps}; one box {32 pixels, 8 dx, 9 k}
+// = 9216 B is everything one warp needs for one dy of one 32-pixel row segment.  (TMA wants the box to
+// start on 16 bytes: when W is not a multiple of 4 the box is 36 pixels wide, starts at the aligned-down
+// pixel and the lanes read at the remainder.)  Each warp of a persistent CTA owns a two-slot ring of such
+// boxes and is its own producer: it issues the box of its next work item, then computes the current one,
+// so ~12 x 9 KB are always in flight per SM and the loads cost one instruction each.  A lane ends up
+// holding the 8 dx of one x for both flow channels = two 32-byte runs of the fine image, which move as
+// 256-bit accesses; nothing is staged for the output.
+template <int kBoxW>
+struct UpCfg {
+  static constexpr int kWarps = kBoxW == 32 ? 12 : 10;
+  static constexpr int kBoxBytes = 9 * 8 * kBoxW * 4;
+  static constexpr int kSmem = kWarps * 2 * kBoxBytes + kWarps * 2 * 8;
+};
 
 __device__ __forceinline__ void st_v8(float* dst, const float (&a)[8]) {
   asm volatile("st.global.L1::no_allocate.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "f"(a[0]),
                "f"(a[1]), "f"(a[2]), "f"(a[3]), "f"(a[4]), "f"(a[5]), "f"(a[6]), "f"(a[7])
                : "memory");
 }
+__device__ __forceinline__ void ld_v8(const float* src, float (&a)[8]) {
+  asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=f"(a[0]), "=f"(a[1]), "=f"(a[2]), "=f"(a[3]), "=f"(a[4]), "=f"(a[5]), "=f"(a[6]), "=f"(a[7])
+               : "l"(src));
+}
 
-__global__ void __launch_bounds__(kUpWarps * 32, 1)
-    upsample_fwd_tma_kernel(const __grid_constant__ CUtensorMap mmap, const float* __restrict__ flow,
-                            float* __restrict__ up, int H, int W, int tiles_x, int n_items) {
+struct UpItem {
+  int n, y, xt, dy;
+};
+__device__ __forceinline__ UpItem decode_item(int it, int tiles_x, int H) {
+  // item = ((n*H + y)*tiles_x + xt)*8 + dy: the warps of a CTA take the 8 dy of one row segment
+  UpItem u;
+  u.dy = it & 7;
+  const int seg = it >> 3;
+  u.xt = seg % tiles_x;
+  const int row = seg / tiles_x;
+  u.y = row % H;
+  u.n = row / H;
+  return u;
+}
+
+template <bool kBwd, int kBoxW>
+__global__ void __launch_bounds__(UpCfg<kBoxW>::kWarps * 32, 1)
+    upsample_tma_kernel(const __grid_constant__ CUtensorMap mmap, const float* __restrict__ flow,
+                        float* __restrict__ up,          // fwd: output; bwd: grad_up (read)
+                        float* __restrict__ gflow, float* __restrict__ gmask, int H, int W, int tiles_x,
+                        int n_items) {
+  using Cfg = UpCfg<kBoxW>;
   extern __shared__ __align__(128) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* ring = reinterpret_cast<float*>(smem + (size_t)warp * 2 * kBoxBytes);
-  const uint32_t bar0 = smem_u32(smem + (size_t)kUpWarps * 2 * kBoxBytes + warp * 16);
+  float* ring = reinterpret_cast<float*>(smem + (size_t)warp * 2 * Cfg::kBoxBytes);
+  const uint32_t bar0 = smem_u32(smem + (size_t)Cfg::kWarps * 2 * Cfg::kBoxBytes + warp * 16);
   if (lane == 0) {
     mbar_init(bar0, 1);
     mbar_init(bar0 + 8, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncwarp();
-  const int stride = gridDim.x * kUpWarps;
-  int item = blockIdx.x * kUpWarps + warp;
-  // item = ((n*H + y)*tiles_x + xt)*8 + dy: the warps of a CTA take the 8 dy of one row segment
+  const int stride = gridDim.x * Cfg::kWarps;
+  int item = blockIdx.x * Cfg::kWarps + warp;
   auto issue = [&](int it, int slot) {
-    const int dy = it & 7, seg = it >> 3;
-    const int xt = seg % tiles_x, row = seg / tiles_x;
-    const int y = row % H, n = row / H;
+    const UpItem u = decode_item(it, tiles_x, H);
     const uint32_t bar = bar0 + slot * 8;
-    mbar_expect_tx(bar, kBoxBytes);
-    tma_load_4d(smem_u32(ring) + slot * kBoxBytes, &mmap, bar, xt * kTileX, y, dy * 8, n * 9);
+    mbar_expect_tx(bar, Cfg::kBoxBytes);
+    tma_load_3d(smem_u32(ring) + slot * Cfg::kBoxBytes, &mmap, bar, (u.y * W + u.xt * kTileX) & ~3, u.dy * 8, u.n * 9);
   };
   if (item < n_items && elect_one()) issue(item, 0);
   uint32_t phases = 0;
+  const size_t cs = (size_t)H * W;
   for (int it = 0; item < n_items; item += stride, ++it) {
     const int slot = it & 1;
     if (item + stride < n_items && elect_one()) issue(item + stride, slot ^ 1);
-    const int dy = item & 7, seg = item >> 3;
-    const int xt = seg % tiles_x, row = seg / tiles_x;
-    const int y = row % H, n = row / H;
-    const int x = xt * kTileX + lane;
+    const UpItem u = decode_item(item, tiles_x, H);
+    const int x = u.xt * kTileX + lane;
+    const bool live = x < W;
     float f0[9], f1[9];
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
-      const int yy = y + k / 3 - 1, xx = x + k % 3 - 1;
+      const int yy = u.y + k / 3 - 1, xx = x + k % 3 - 1;
       const bool in = yy >= 0 && yy < H && xx >= 0 && xx < W;
-      const float* p = flow + ((size_t)(n * 2) * H + yy) * W + xx;
+      const float* p = flow + ((size_t)(u.n * 2) * H + yy) * W + xx;
       f0[k] = in ? 8.0f * __ldg(p) : 0.f;
-      f1[k] = in ? 8.0f * __ldg(p + (size_t)H * W) : 0.f;
+      f1[k] = in ? 8.0f * __ldg(p + cs) : 0.f;
+    }
+    float* fine = up + ((size_t)(u.n * 2) * (8 * H) + 8 * u.y + u.dy) * (8 * W) + 8 * x;
+    const size_t fine_cs = (size_t)(8 * H) * (8 * W);
+    float a0[8], a1[8];  // fwd: results; bwd: incoming gradient of the fine pixels
+    if constexpr (kBwd) {
+#pragma unroll
+      for (int dx = 0; dx < 8; ++dx) a0[dx] = a1[dx] = 0.f;
+      if (live) {
+        ld_v8(fine, a0);
+        ld_v8(fine + fine_cs, a1);
+      }
     }
     mbar_wait(bar0 + slot * 8, (phases >> slot) & 1u);
     phases ^= 1u << slot;
-    const float* box = ring + slot * (kBoxBytes / 4) + lane;
-    float a0[8], a1[8];
+    const int rem = kBoxW == 32 ? 0 : ((u.y * W + u.xt * kTileX) & 3);
+    const float* box = ring + slot * (Cfg::kBoxBytes / 4) + rem + lane;
+    float t0[9], t1[9];
+    if constexpr (kBwd) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) t0[k] = t1[k] = 0.f;
+    }
+    float* gm = kBwd && gmask ? gmask + ((size_t)u.n * 576 + u.dy * 8) * cs + (size_t)u.y * W + x : nullptr;
 #pragma unroll
     for (int dx = 0; dx < 8; ++dx) {
       float v[9];
 #pragma unroll
-      for (int k = 0; k < 9; ++k) v[k] = box[(k * 8 + dx) * kTileX];
+      for (int k = 0; k < 9; ++k) v[k] = box[(k * 8 + dx) * kBoxW];
       float mx = v[0];
 #pragma unroll
       for (int k = 1; k < 9; ++k) mx = fmaxf(mx, v[k]);
       constexpr float kLog2e = 1.4426950408889634f;
-      float s = 0.f, b0 = 0.f, b1 = 0.f;
+      float s = 0.f;
 #pragma unroll
       for (int k = 0; k < 9; ++k) {
-        const float e = exp2f((v[k] - mx) * kLog2e);  // v - mx first: the largest tap is exactly 1
-        s += e;
-        b0 = fmaf(e, f0[k], b0);
-        b1 = fmaf(e, f1[k], b1);
+        v[k] = exp2f((v[k] - mx) * kLog2e);  // v - mx first: the largest tap is exactly 1
+        s += v[k];
       }
       const float inv = __frcp_rn(s);
-      a0[dx] = b0 * inv;
-      a1[dx] = b1 * inv;
+      if constexpr (!kBwd) {
+        float b0 = 0.f, b1 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+          b0 = fmaf(v[k], f0[k], b0);
+          b1 = fmaf(v[k], f1[k], b1);
+        }
+        a0[dx] = b0 * inv;
+        a1[dx] = b1 * inv;
+      } else {
+        const float g0 = a0[dx], g1 = a1[dx];
+        float gk[9], dot = 0.f;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+          v[k] *= inv;
+          gk[k] = fmaf(g0, f0[k], g1 * f1[k]);
+          dot = fmaf(v[k], gk[k], dot);
+          t0[k] = fmaf(v[k], g0, t0[k]);
+          t1[k] = fmaf(v[k], g1, t1[k]);
+        }
+        if (gm && live) {
+#pragma unroll
+          for (int k = 0; k < 9; ++k) __stcs(gm + (size_t)(k * 64 + dx) * cs, v[k] * (gk[k] - dot));
+        }
+      }
     }
     __syncwarp();  // every lane is done with this slot before the next iteration refills it
-    if (x < W) {
-      float* dst = up + ((size_t)(n * 2) * (8 * H) + 8 * y + dy) * (8 * W) + 8 * x;
-      st_v8(dst, a0);
-      st_v8(dst + (size_t)(8 * H) * (8 * W), a1);
+    if constexpr (!kBwd) {
+      if (live) {
+        st_v8(fine, a0);
+        st_v8(fine + fine_cs, a1);
+      }
+    } else if (gflow) {
+      // coarse pixel P gets tap kx=0 of lane P+1, kx=1 of lane P and kx=2 of lane P-1 (dead lanes hold 0)
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const int yy = u.y + ky - 1;
+        const bool row_ok = yy >= 0 && yy < H;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const float l = c ? t1[ky * 3 + 0] : t0[ky * 3 + 0];
+          const float m = c ? t1[ky * 3 + 1] : t0[ky * 3 + 1];
+          const float r = c ? t1[ky * 3 + 2] : t0[ky * 3 + 2];
+          const float from_right = __shfl_down_sync(0xffffffffu, l, 1);
+          const float from_left = __shfl_up_sync(0xffffffffu, r, 1);
+          float sum = m + (lane < 31 ? from_right : 0.f) + (lane > 0 ? from_left : 0.f);
+          if (!row_ok) continue;
+          float* dst = gflow + ((size_t)(u.n * 2 + c) * H + yy) * W;
+          if (live) atomicAdd(dst + x, 8.0f * sum);
+          if (lane == 0 && x > 0) atomicAdd(dst + x - 1, 8.0f * l);
+          if (lane == 31 && x + 1 < W) atomicAdd(dst + x + 1, 8.0f * r);
+        }
+      }
     }
   }
 }
@@ -296,33 +382,50 @@ __global__ void __launch_bounds__(256) upflow8_kernel(const float* __restrict__ 
   __stcs(reinterpret_cast<float4*>(up) + i, make_float4(o[0], o[1], o[2], o[3]));
 }
 
+
+template <bool kBwd, int kBoxW>
+int launch_upsample_tma(const float* flow, const float* mask, float* fine, float* gflow, float* gmask, int B, int H,
+                        int W, long long items, cudaStream_t stream) {
+  using Cfg = UpCfg<kBoxW>;
+  CUtensorMap m;
+  const cuuint64_t dims[3] = {(cuuint64_t)H * W, 64, (cuuint64_t)9 * B};
+  const cuuint64_t strides[2] = {(cuuint64_t)H * W * 4, (cuuint64_t)64 * H * W * 4};
+  const cuuint32_t box[3] = {kBoxW, 8, 9};
+  if (int rc = encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(mask), dims, strides, box,
+                      CU_TENSOR_MAP_SWIZZLE_NONE, "upsample mask", CU_TENSOR_MAP_L2_PROMOTION_NONE))
+    return rc;
+  int dev = 0, sms = 0;
+  RC_CHECK_CUDA(cudaGetDevice(&dev));
+  RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  static std::atomic<unsigned long long> configured{0};  // one bit per device (per instantiation)
+  if (!(configured.load() >> dev & 1ull)) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(upsample_tma_kernel<kBwd, kBoxW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::kSmem));
+    configured.fetch_or(1ull << dev);
+  }
+  const int grid = (int)std::min<long long>(sms, (items + Cfg::kWarps - 1) / Cfg::kWarps);
+  upsample_tma_kernel<kBwd, kBoxW><<<grid, Cfg::kWarps * 32, Cfg::kSmem, stream>>>(
+      m, flow, fine, gflow, gmask, H, W, (W + kTileX - 1) / kTileX, (int)items);
+  RC_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// TMA path: 16-byte channel stride, 16-byte mask base, 32-byte fine rows; dev < 64 for the attribute bitmap
+bool upsample_tma_ok(const float* mask, const float* fine, int H, int W, long long items) {
+  int dev = 0;
+  return ((long long)H * W) % 4 == 0 && !(reinterpret_cast<uintptr_t>(mask) & 15) &&
+         !(reinterpret_cast<uintptr_t>(fine) & 31) && items < (1ll << 30) && (long long)H * W < (1ll << 31) &&
+         cudaGetDevice(&dev) == cudaSuccess && dev < 64 && get_encode() != nullptr;
+}
+
 }  // namespace
 
 int launch_upsample_fwd(const float* flow, const float* mask, float* up, int B, int H, int W, cudaStream_t stream) {
   if (B == 0) return 0;
   const long long items = (long long)B * H * ((W + kTileX - 1) / kTileX) * 8;
-  if (W % 4 == 0 && !(reinterpret_cast<uintptr_t>(mask) & 15) && !(reinterpret_cast<uintptr_t>(up) & 31) &&
-      items < (1ll << 30) && get_encode()) {
-    CUtensorMap m;
-    const cuuint64_t dims[4] = {(cuuint64_t)W, (cuuint64_t)H, 64, (cuuint64_t)9 * B};
-    const cuuint64_t strides[3] = {(cuuint64_t)W * 4, (cuuint64_t)H * W * 4, (cuuint64_t)64 * H * W * 4};
-    const cuuint32_t box[4] = {kTileX, 1, 8, 9};
-    if (int rc = encode(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(mask), dims, strides, box,
-                        CU_TENSOR_MAP_SWIZZLE_NONE, "upsample mask", CU_TENSOR_MAP_L2_PROMOTION_NONE))
-      return rc;
-    int dev = 0, sms = 0;
-    RC_CHECK_CUDA(cudaGetDevice(&dev));
-    RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    static std::atomic<unsigned long long> configured{0};  // one bit per device
-    if (!(configured.load() >> dev & 1ull)) {
-      RC_CHECK_CUDA(cudaFuncSetAttribute(upsample_fwd_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kUpSmem));
-      configured.fetch_or(1ull << dev);
-    }
-    const int grid = (int)std::min<long long>(sms, (items + kUpWarps - 1) / kUpWarps);
-    upsample_fwd_tma_kernel<<<grid, kUpWarps * 32, kUpSmem, stream>>>(m, flow, up, H, W, (W + kTileX - 1) / kTileX,
-                                                                    (int)items);
-    RC_CHECK_CUDA(cudaGetLastError());
-    return 0;
+  if (upsample_tma_ok(mask, up, H, W, items)) {
+    if (W % 4 == 0) return launch_upsample_tma<false, 32>(flow, mask, up, nullptr, nullptr, B, H, W, items, stream);
+    return launch_upsample_tma<false, 36>(flow, mask, up, nullptr, nullptr, B, H, W, items, stream);
   }
   dim3 grid((W + kTileX - 1) / kTileX, H, B);
   upsample_fwd_kernel<<<grid, kThreads, 0, stream>>>(flow, mask, up, H, W);
@@ -334,6 +437,12 @@ int launch_upsample_bwd(const float* flow, const float* mask, const float* gup, 
                         int H, int W, cudaStream_t stream) {
   if (B == 0) return 0;
   if (gflow) RC_CHECK_CUDA(cudaMemsetAsync(gflow, 0, sizeof(float) * 2 * (size_t)B * H * W, stream));
+  const long long items = (long long)B * H * ((W + kTileX - 1) / kTileX) * 8;
+  if (upsample_tma_ok(mask, gup, H, W, items) && (!gmask || !(reinterpret_cast<uintptr_t>(gmask) & 3))) {
+    float* g = const_cast<float*>(gup);  // read-only in the backward instantiation
+    if (W % 4 == 0) return launch_upsample_tma<true, 32>(flow, mask, g, gflow, gmask, B, H, W, items, stream);
+    return launch_upsample_tma<true, 36>(flow, mask, g, gflow, gmask, B, H, W, items, stream);
+  }
   dim3 grid((W + kTileX - 1) / kTileX, H, B);
   upsample_bwd_kernel<<<grid, kThreads, 0, stream>>>(flow, mask, gup, gflow, gmask, H, W);
   RC_CHECK_CUDA(cudaGetLastError());

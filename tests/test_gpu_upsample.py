@@ -32,7 +32,7 @@ def test_backward_matches_reference_golden(golden):
         assert np.allclose(got.cpu().numpy(), ref, rtol=1e-3, atol=1e-4 * np.abs(ref).max())
 
 
-@pytest.mark.parametrize("B,H,W", [(1, 1, 1), (1, 3, 33), (2, 5, 64), (1, 46, 62), (2, 55, 128)])
+@pytest.mark.parametrize("B,H,W", [(1, 1, 1), (1, 3, 33), (2, 5, 64), (1, 46, 62), (2, 55, 128), (1, 6, 34), (1, 47, 156)])
 def test_forward_matches_oracle(B, H, W):
     import upsample
     gen = torch.Generator().manual_seed(H * 1000 + W)
@@ -44,11 +44,12 @@ def test_forward_matches_oracle(B, H, W):
     assert rel_max(upsample.upflow8(flow.cuda()).cpu().numpy(), oracle.upflow8(flow)) <= 1e-5
 
 
-def test_backward_matches_autograd_of_restatement():
-    """cfg5 shape (46x62): grads against torch autograd through the reference's op sequence on the GPU."""
+@pytest.mark.parametrize("B,H,W", [(3, 46, 62), (2, 17, 128), (1, 5, 7), (2, 6, 34)])
+def test_backward_matches_autograd_of_restatement(B, H, W):
+    """cfg5 shape (46x62, the 36-wide boxes), a 32-wide-box shape, and two that take the plain-load kernels:
+    grads against torch autograd through the reference's op sequence on the GPU."""
     import upsample
     gen = torch.Generator().manual_seed(77)
-    B, H, W = 3, 46, 62
     flow = (5 * torch.randn(B, 2, H, W, generator=gen)).cuda()
     mask = (3 * torch.randn(B, 576, H, W, generator=gen)).cuda()
     gup = torch.randn(B, 2, 8 * H, 8 * W, generator=gen).cuda()
