@@ -163,35 +163,60 @@ __global__ void __launch_bounds__(UpCfg<kBoxW>::kWarps * 32, 1)
     mbar_expect_tx(bar, Cfg::kBoxBytes);
     tma_load_3d(smem_u32(ring) + slot * Cfg::kBoxBytes, &mmap, bar, (u.y * W + u.xt * kTileX) & ~3, u.dy * 8, u.n * 9);
   };
-  if (item < n_items && elect_one()) issue(item, 0);
-  uint32_t phases = 0;
   const size_t cs = (size_t)H * W;
-  for (int it = 0; item < n_items; item += stride, ++it) {
-    const int slot = it & 1;
-    if (item + stride < n_items && elect_one()) issue(item + stride, slot ^ 1);
-    const UpItem u = decode_item(item, tiles_x, H);
+  // 8*flow of the 3x3 coarse neighbours of this lane's pixel (zero outside: F.unfold(padding=1)); fetched one
+  // item ahead like the mask box, so that the L2 round trip is hidden behind the current item's arithmetic
+  auto load_flow = [&](int it, float (&f0)[9], float (&f1)[9]) {
+    const UpItem u = decode_item(it, tiles_x, H);
     const int x = u.xt * kTileX + lane;
-    const bool live = x < W;
-    float f0[9], f1[9];
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
       const int yy = u.y + k / 3 - 1, xx = x + k % 3 - 1;
       const bool in = yy >= 0 && yy < H && xx >= 0 && xx < W;
       const float* p = flow + ((size_t)(u.n * 2) * H + yy) * W + xx;
-      f0[k] = in ? 8.0f * __ldg(p) : 0.f;
-      f1[k] = in ? 8.0f * __ldg(p + cs) : 0.f;
+      f0[k] = in ? __ldg(p) : 0.f;
+      f1[k] = in ? __ldg(p + cs) : 0.f;
     }
-    float* fine = up + ((size_t)(u.n * 2) * (8 * H) + 8 * u.y + u.dy) * (8 * W) + 8 * x;
-    const size_t fine_cs = (size_t)(8 * H) * (8 * W);
-    float a0[8], a1[8];  // fwd: results; bwd: incoming gradient of the fine pixels
-    if constexpr (kBwd) {
+  };
+  const size_t fine_cs = (size_t)(8 * H) * (8 * W);
+  auto fine_ptr = [&](const UpItem& u, int x) {
+    return up + ((size_t)(u.n * 2) * (8 * H) + 8 * u.y + u.dy) * (8 * W) + 8 * x;
+  };
+  // backward only: the incoming gradient of this lane's 8 fine pixels per channel, also one item ahead
+  auto load_grad = [&](int it, float (&g0)[8], float (&g1)[8]) {
+    const UpItem u = decode_item(it, tiles_x, H);
+    const int x = u.xt * kTileX + lane;
 #pragma unroll
-      for (int dx = 0; dx < 8; ++dx) a0[dx] = a1[dx] = 0.f;
-      if (live) {
-        ld_v8(fine, a0);
-        ld_v8(fine + fine_cs, a1);
-      }
+    for (int dx = 0; dx < 8; ++dx) g0[dx] = g1[dx] = 0.f;
+    if (x < W) {
+      ld_v8(fine_ptr(u, x), g0);
+      ld_v8(fine_ptr(u, x) + fine_cs, g1);
     }
+  };
+  float f0[9], f1[9], a0[8], a1[8];  // a: forward results / backward incoming gradient
+  if (item < n_items) {
+    if (elect_one()) issue(item, 0);
+    load_flow(item, f0, f1);
+    if constexpr (kBwd) load_grad(item, a0, a1);
+  }
+  uint32_t phases = 0;
+  for (int it = 0; item < n_items; item += stride, ++it) {
+    const int slot = it & 1;
+    float nf0[9], nf1[9], na0[8], na1[8];
+    if (item + stride < n_items) {
+      if (elect_one()) issue(item + stride, slot ^ 1);
+      load_flow(item + stride, nf0, nf1);
+      if constexpr (kBwd) load_grad(item + stride, na0, na1);
+    }
+    const UpItem u = decode_item(item, tiles_x, H);
+    const int x = u.xt * kTileX + lane;
+    const bool live = x < W;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      f0[k] *= 8.0f;
+      f1[k] *= 8.0f;
+    }
+    float* fine = fine_ptr(u, x);
     mbar_wait(bar0 + slot * 8, (phases >> slot) & 1u);
     phases ^= 1u << slot;
     const int rem = kBoxW == 32 ? 0 : ((u.y * W + u.xt * kTileX) & 3);
@@ -270,6 +295,18 @@ __global__ void __launch_bounds__(UpCfg<kBoxW>::kWarps * 32, 1)
           if (lane == 0 && x > 0) atomicAdd(dst + x - 1, 8.0f * l);
           if (lane == 31 && x + 1 < W) atomicAdd(dst + x + 1, 8.0f * r);
         }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      f0[k] = nf0[k];
+      f1[k] = nf1[k];
+    }
+    if constexpr (kBwd) {
+#pragma unroll
+      for (int dx = 0; dx < 8; ++dx) {
+        a0[dx] = na0[dx];
+        a1[dx] = na1[dx];
       }
     }
   }
