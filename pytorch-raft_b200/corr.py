@@ -74,8 +74,9 @@ class AlternateCorrBlock:
     ``precision='bf16'`` (default without autograd): one fused tensor-core launch per call — the
     windows of a tile of 128 neighbouring queries overlap, so their union is a small dense GEMM
     against bf16 NHWC copies of fmap1 and the pooled fmap2 pyramid (csrc/alt_tc.cu); the 1/sqrt(D) of
-    corr.py:91 and the /2^l of corr.py:85 are folded in.  ``precision='fp32'`` (and any call that
-    needs gradients): one fp32 CUDA-core launch per level (csrc/alt.cu), differentiable.
+    corr.py:91 and the /2^l of corr.py:85 are folded in; with autograd the backward runs the fp32
+    per-level kernels.  ``precision='fp32'``: one fp32 CUDA-core launch per level (csrc/alt.cu),
+    differentiable.
 
     ``coord_mode`` defaults to CorrBlock's coordinate semantics so both blocks produce identical
     zero-padding masks; pass 'direct' for the reference CUDA kernel's floor(coords) behaviour
@@ -108,6 +109,9 @@ class AlternateCorrBlock:
                                              or self._f2[0].requires_grad)
         if self._f1_bf16 is not None and not graph:
             return ops.alt_fused_forward(self._f1_bf16, self._f2_bf16, coords, self.radius, self._coord_mode, scale)
+        if self._f1_bf16 is not None:
+            holder = {"f1_bf16": self._f1_bf16, "f2_bf16": self._f2_bf16}
+            return ops.AltFusedFn.apply(coords, self._f1, holder, self.radius, self._coord_mode, scale, *self._f2)
         coords = coords.permute(0, 2, 3, 1)
         B, H, W, _ = coords.shape
         corr_list = []

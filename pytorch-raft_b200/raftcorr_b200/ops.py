@@ -296,6 +296,38 @@ class AltFn(torch.autograd.Function):
         return g1, g2, gc, None, None, None
 
 
+class AltFusedFn(torch.autograd.Function):
+    """All levels of the on-the-fly path in one tensor-core launch (bf16 products), differentiable: the
+    backward runs the fp32 per-level kernels on the fp32 feature maps (it does not need the forward's output,
+    the op is bilinear in the feature maps)."""
+
+    @staticmethod
+    def forward(ctx, coords, fmap1, holder, radius, coord_mode, scale, *fmap2_levels):
+        ctx.radius, ctx.coord_mode, ctx.scale = radius, coord_mode, scale
+        ctx.save_for_backward(coords, fmap1, *fmap2_levels)
+        return alt_fused_forward(holder["f1_bf16"], holder["f2_bf16"], coords, radius, coord_mode, scale)
+
+    @staticmethod
+    def backward(ctx, grad):
+        coords, fmap1, *levels = ctx.saved_tensors
+        B, _, H, W = coords.shape
+        win = (2 * ctx.radius + 1) ** 2
+        want_coords = ctx.needs_input_grad[0]
+        base = coords.permute(0, 2, 3, 1)
+        g1_total, gc_total, g2 = None, None, []
+        for l, f2 in enumerate(levels):
+            coords_l = (base / 2 ** l).reshape(B, 1, H, W, 2).contiguous()
+            g_l = grad[:, l * win:(l + 1) * win].reshape(B, 1, win, H, W).contiguous()
+            g1, g2_l, gc = alt_backward(fmap1, f2, coords_l, g_l, ctx.radius, ctx.coord_mode, ctx.scale,
+                                        want_coords=want_coords)
+            g1_total = g1 if g1_total is None else g1_total.add_(g1)
+            g2.append(g2_l)
+            if want_coords:
+                gc = gc.reshape(B, H, W, 2).permute(0, 3, 1, 2) / 2 ** l
+                gc_total = gc if gc_total is None else gc_total + gc
+        return (gc_total.contiguous() if want_coords else None, g1_total, None, None, None, None, *g2)
+
+
 # ---- the step after the path: flow upsampling (SURVEY.md §8f-4) ------------------------------------
 
 def _check_flow_mask(flow: torch.Tensor, mask: Optional[torch.Tensor]):

@@ -166,8 +166,10 @@ def test_alt_cuda_corr_module_surface(golden):
     assert isinstance(grads, list) and [tuple(t.shape) for t in grads] == [tuple(f1.shape), tuple(f2.shape), tuple(c.shape)]
 
 
-def test_alternate_corr_block_backward():
-    """Gradients of the on-the-fly path vs autograd through its torch restatement (CPU)."""
+@pytest.mark.parametrize("precision", [None, "fp32"])
+def test_alternate_corr_block_backward(precision):
+    """Gradients of the on-the-fly path vs autograd through its torch restatement (CPU): the default block
+    (fused tensor-core forward, fp32 per-level backward) and the all-fp32 one."""
     import corr
     gen = torch.Generator().manual_seed(8)
     B, D, H, W = 1, 16, 16, 24
@@ -179,7 +181,10 @@ def test_alternate_corr_block_backward():
     a, b_, cc = f1.clone().requires_grad_(True), f2.clone().requires_grad_(True), c.clone().requires_grad_(True)
     tr.alt_corr_block_math(a, b_, cc, 4, 4).backward(up)
     x, y, z = f1.cuda().requires_grad_(True), f2.cuda().requires_grad_(True), c.cuda().requires_grad_(True)
-    out = corr.AlternateCorrBlock(x, y, coord_mode="direct")(z)
+    out = corr.AlternateCorrBlock(x, y, coord_mode="direct", precision=precision)(z)
+    with torch.no_grad():
+        plain = corr.AlternateCorrBlock(x, y, coord_mode="direct", precision=precision)(z)
+    assert torch.equal(out, plain)   # recording a graph does not change the forward values
     out.backward(up.cuda())
     for got, ref in ((x.grad, a.grad), (y.grad, b_.grad), (z.grad, cc.grad)):
         ref = ref.numpy()

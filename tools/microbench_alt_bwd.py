@@ -45,3 +45,19 @@ if which in ("all", "bwd"):
     print(f"  lookup_bwd (scatter): {ms*1e3:.1f} us")
     ms = timeit(lambda: ops.build_backward(gp, f1.detach(), f2.detach()), reps=3)
     print(f"  build_bwd (unpool + 2 fp32 GEMMs): {ms:.2f} ms  {4*B*(H*W)**2*D/ms/1e9:.1f} TFLOP/s")
+if which in ("all", "altbwd"):
+    B, D, H, W = 12, 256, 46, 62    # training shape, on-the-fly block with autograd (fp32 per-level kernels)
+    f1 = torch.randn(B, D, H, W, device="cuda", requires_grad=True); f2 = torch.randn(B, D, H, W, device="cuda", requires_grad=True)
+    c = grid(B, H, W) + 4 * torch.randn(B, 2, H, W, device="cuda")
+    blk = corr.AlternateCorrBlock(f1, f2)
+    out = blk(c)
+    go = torch.randn_like(out)
+    ms_f = timeit(lambda: blk(c), reps=3, warm=1)
+    def fb():
+        f1.grad = None; f2.grad = None
+        corr.AlternateCorrBlock(f1, f2)(c).backward(go)
+    ms_fb = timeit(fb, reps=3, warm=1)
+    print(f"alt (autograd: fused TC forward, fp32 per-level backward) B=12 46x62: fwd {ms_f:.2f} ms, fwd+bwd {ms_fb:.2f} ms per iteration")
+    with torch.no_grad():
+        ms = timeit(lambda: corr.AlternateCorrBlock(f1.detach(), f2.detach())(c), reps=3, warm=1)
+    print(f"alt (no grad, fused bf16 TC incl. constructor) same shape: {ms:.3f} ms")
