@@ -70,6 +70,96 @@ class Encoder(nn.Module):
         return self.conv2(x)
 
 
+class NarrowBlock(nn.Module):
+    """extractor.py:58-116 (BottleneckBlock): 1x1 -> 3x3 (strided) -> 1x1 at a quarter of the width, with a
+    strided 1x1 skip when the resolution changes."""
+
+    def __init__(self, cin: int, cout: int, norm: str, stride: int):
+        super().__init__()
+        mid = cout // 4
+        self.conv1 = nn.Conv2d(cin, mid, 1)
+        self.conv2 = nn.Conv2d(mid, mid, 3, padding=1, stride=stride)
+        self.conv3 = nn.Conv2d(mid, cout, 1)
+        self.norm1, self.norm2, self.norm3 = _norm(norm, mid), _norm(norm, mid), _norm(norm, cout)
+        self.downsample = None
+        if stride != 1:
+            self.norm4 = _norm(norm, cout)
+            self.downsample = nn.Sequential(nn.Conv2d(cin, cout, 1, stride=stride), self.norm4)
+
+    def forward(self, x):
+        y = F.relu(self.norm1(self.conv1(x)))
+        y = F.relu(self.norm2(self.conv2(y)))
+        y = F.relu(self.norm3(self.conv3(y)))
+        skip = x if self.downsample is None else self.downsample(x)
+        return F.relu(skip + y)
+
+
+class SmallEncoder(nn.Module):
+    """extractor.py:195-267: the 1/8-resolution encoder of the small model (32-64-96 bottleneck stages)."""
+
+    def __init__(self, out_dim: int, norm: str):
+        super().__init__()
+        self.conv1 = nn.Conv2d(3, 32, 7, stride=2, padding=3)
+        self.norm1 = _norm(norm, 32)
+        cin = 32
+        for idx, (w, stride) in enumerate(((32, 1), (64, 2), (96, 2)), start=1):
+            setattr(self, f"layer{idx}", nn.Sequential(NarrowBlock(cin, w, norm, stride), NarrowBlock(w, w, norm, 1)))
+            cin = w
+        self.conv2 = nn.Conv2d(96, out_dim, 1)
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+
+    def forward(self, x):
+        x = F.relu(self.norm1(self.conv1(x)))
+        return self.conv2(self.layer3(self.layer2(self.layer1(x))))
+
+
+class SmallMotionEncoder(nn.Module):
+    """update.py:62-77: consumes the 196-channel lookup of the small model."""
+
+    def __init__(self, corr_channels: int):
+        super().__init__()
+        self.convc1 = nn.Conv2d(corr_channels, 96, 1)
+        self.convf1 = nn.Conv2d(2, 64, 7, padding=3)
+        self.convf2 = nn.Conv2d(64, 32, 3, padding=1)
+        self.conv = nn.Conv2d(128, 80, 3, padding=1)
+
+    def forward(self, flow, corr):
+        c = F.relu(self.convc1(corr))
+        f = F.relu(self.convf2(F.relu(self.convf1(flow))))
+        return torch.cat([F.relu(self.conv(torch.cat([c, f], dim=1))), flow], dim=1)
+
+
+class GRU3x3(nn.Module):
+    """update.py:16-31 (ConvGRU): one 3x3 convolutional GRU step."""
+
+    def __init__(self, hidden: int, inp: int):
+        super().__init__()
+        for gate in "zrq":
+            setattr(self, "conv" + gate, nn.Conv2d(hidden + inp, hidden, 3, padding=1))
+
+    def forward(self, h, x):
+        hx = torch.cat([h, x], dim=1)
+        z, r = torch.sigmoid(self.convz(hx)), torch.sigmoid(self.convr(hx))
+        q = torch.tanh(self.convq(torch.cat([r * h, x], dim=1)))
+        return (1 - z) * h + z * q
+
+
+class SmallUpdateBlock(nn.Module):
+    """update.py:99-111: no upsampling mask (the small model upsamples bilinearly, raft.py:134-135)."""
+
+    def __init__(self, corr_channels: int, hidden: int = 96):
+        super().__init__()
+        self.encoder = SmallMotionEncoder(corr_channels)
+        self.gru = GRU3x3(hidden, 82 + 64)
+        self.flow_head = FlowHead(hidden, 128)
+
+    def forward(self, net, inp, corr, flow):
+        net = self.gru(net, torch.cat([inp, self.encoder(flow, corr)], dim=1))
+        return net, None, self.flow_head(net)
+
+
 class MotionEncoder(nn.Module):
     """update.py:79-97: consumes the 324-channel lookup (convc1 is a 1x1 conv 324->256)."""
 
@@ -148,16 +238,29 @@ def convex_upsample(flow: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
     return up.permute(0, 1, 4, 2, 5, 3).reshape(B, 2, 8 * H, 8 * W)
 
 
+def bilinear_upsample8(flow: torch.Tensor) -> torch.Tensor:
+    """utils.py:80-82 (upflow8)."""
+    return 8 * F.interpolate(flow, size=(8 * flow.shape[2], 8 * flow.shape[3]), mode="bilinear", align_corners=True)
+
+
 class StockRAFT(nn.Module):
-    """raft.py:24-144 for the non-small model (hidden 128, context 128, 4 levels, radius 4)."""
+    """raft.py:24-144.  Default: the basic model (hidden 128, context 128, 4 levels, radius 4, D=256);
+    ``small=True``: raft.py:29-33,49-51 (hidden 96, context 64, radius 3, D=128, 196 lookup channels, bilinear
+    upsampling)."""
 
-    levels, radius, hidden, context = 4, 4, 128, 128
-
-    def __init__(self):
+    def __init__(self, small: bool = False):
         super().__init__()
-        self.fnet = Encoder(256, "instance")
-        self.cnet = Encoder(self.hidden + self.context, "batch")
-        self.update_block = UpdateBlock(self.levels * (2 * self.radius + 1) ** 2, self.hidden)
+        self.small, self.levels = small, 4
+        if small:
+            self.radius, self.hidden, self.context = 3, 96, 64
+            self.fnet = SmallEncoder(128, "instance")
+            self.cnet = SmallEncoder(self.hidden + self.context, "none")
+            self.update_block = SmallUpdateBlock(self.levels * (2 * self.radius + 1) ** 2, self.hidden)
+        else:
+            self.radius, self.hidden, self.context = 4, 128, 128
+            self.fnet = Encoder(256, "instance")
+            self.cnet = Encoder(self.hidden + self.context, "batch")
+            self.update_block = UpdateBlock(self.levels * (2 * self.radius + 1) ** 2, self.hidden)
 
     def features(self, image1, image2):
         """raft.py:89-103 + 110-114: normalise, encode both frames in one batch, context split."""
@@ -169,11 +272,12 @@ class StockRAFT(nn.Module):
         return fmap1.float(), fmap2.float(), torch.tanh(net), torch.relu(inp)
 
     def forward(self, image1, image2, corr_factory, iters: int = 12, flow_init=None, lookup_hook=None,
-                upsampler=None):
+                upsampler=None, upsampler8=None):
         """Returns (flow at 1/8 resolution, upsampled flow) like raft.py's test_mode.  ``upsampler(flow, mask)``
         replaces raft.py:72-83 (default: the stock-torch op sequence); like the reference it runs after
         every iteration (raft.py:134-139)."""
         upsampler = upsampler or convex_upsample
+        upsampler8 = upsampler8 or bilinear_upsample8
         fmap1, fmap2, net, inp = self.features(image1, image2)
         corr_fn = corr_factory(fmap1, fmap2, self.radius)
         B, _, H, W = fmap1.shape
@@ -185,5 +289,6 @@ class StockRAFT(nn.Module):
             corr = corr_fn(coords1) if lookup_hook is None else lookup_hook(corr_fn, coords1)
             net, up_mask, delta = self.update_block(net, inp, corr, coords1 - coords0)
             coords1 = coords1 + delta
-            flow_up = upsampler(coords1 - coords0, up_mask)
+            flow = coords1 - coords0
+            flow_up = upsampler8(flow) if up_mask is None else upsampler(flow, up_mask)
         return coords1 - coords0, flow_up

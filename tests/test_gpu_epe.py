@@ -47,3 +47,26 @@ def test_twelve_iteration_flow_epe(shape):
     lo, up = _flows(model, im1[:1], im2[:1], lambda a, b, r: corr.AlternateCorrBlock(a, b, radius=r))
     epe = (up - up_ref[:1]).pow(2).sum(1).sqrt().mean().item()
     assert epe <= 0.01, ("alternate", epe)
+
+
+def test_small_model_flow_epe():
+    """The --small configuration (raft.py:29-33,49-51: radius 3, D=128, 196 lookup channels, sqrt(128) inexact,
+    bilinear upflow8): same 0.01 px bar, with the library's upflow8 kernel in place of utils.py:80-82."""
+    import corr
+    import upsample
+    torch.manual_seed(4321)
+    model = StockRAFT(small=True).eval().cuda()
+    gen = torch.Generator().manual_seed(18)
+    im1 = (torch.rand(2, 3, 368, 496, generator=gen) * 255).cuda()
+    im2 = (torch.rand(2, 3, 368, 496, generator=gen) * 255).cuda()
+    lo_ref, up_ref = _flows(model, im1, im2, lambda a, b, r: tr.TorchCorrBlock(a, b, 4, r))
+    assert up_ref.pow(2).sum(1).sqrt().mean().item() > 0.05
+    for precision in ("fp32", "bf16"):
+        with torch.no_grad():
+            lo, up = model(im1, im2, lambda a, b, r: corr.CorrBlock(a, b, radius=r, precision=precision), iters=12,
+                           upsampler8=upsample.upflow8)
+        assert lo.shape == (2, 2, 46, 62) and up.shape == (2, 2, 368, 496)
+        epe = (up - up_ref).pow(2).sum(1).sqrt().mean().item()
+        assert epe <= 0.01, (precision, epe)
+    lo, up = _flows(model, im1, im2, lambda a, b, r: corr.AlternateCorrBlock(a, b, radius=r))
+    assert (up - up_ref).pow(2).sum(1).sqrt().mean().item() <= 0.01

@@ -14,7 +14,8 @@ REF = "/root/reference/core"
 
 
 @pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree not present")
-def test_harness_matches_reference_model():
+@pytest.mark.parametrize("small", [False, True])
+def test_harness_matches_reference_model(small):
     from harness.raft_stock import StockRAFT
     from oracle import torch_restatement as tr
 
@@ -24,8 +25,8 @@ def test_harness_matches_reference_model():
     try:
         from raft import RAFT
         torch.manual_seed(1234)
-        ref = RAFT(argparse.Namespace(small=False, mixed_precision=False, alternate_corr=False)).eval()
-        mine = StockRAFT().eval()
+        ref = RAFT(argparse.Namespace(small=small, mixed_precision=False, alternate_corr=False)).eval()
+        mine = StockRAFT(small=small).eval()
         missing = mine.load_state_dict(ref.state_dict(), strict=True)
         assert not missing.missing_keys and not missing.unexpected_keys
         gen = torch.Generator().manual_seed(5)
