@@ -38,8 +38,17 @@ for _p in (ROOT, PKG):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
-# NCCL writes its banner / debug lines to stdout by default; stdout is reserved for the one JSON line
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout is reserved for the one JSON line, but libraries write there too (NCCL prints its version banner with
+# printf).  Keep a private duplicate of the real stdout for the result and point fd 1 at stderr for everyone else.
+sys.stdout.flush()
+_RESULT_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    sys.stdout.flush()
+    os.write(_RESULT_FD, (json.dumps(line) + "\n").encode())
+
 
 import torch  # noqa: E402
 
@@ -248,7 +257,7 @@ def main():
                                  "sample": ref["sample"]},
                 "e2e": {"value": ref["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line))
+        emit(line)
         return
 
     assert torch.cuda.is_available(), "bench.py (impl ours) needs CUDA devices; there is no CPU fallback"
@@ -433,7 +442,7 @@ def main():
         ref = run_cpu_reference(steps=1, warmup=1)
         line["cpu_baseline"] = {"value": ref["value"], "unit": UNIT, "cores": ref["cores"], "kind": ref["kind"],
                                 "sample": ref["sample"]}
-    print(json.dumps(line))
+    emit(line)
     if distributed:
         dist.destroy_process_group()
 
