@@ -41,3 +41,34 @@ def test_random_shape_end_to_end(B, D, H, W, r, kind):
             alt = corr.AlternateCorrBlock(f1.cuda(), f2.cuda(), radius=r, precision=precision)(c.cuda()).cpu().numpy()
             assert np.array_equal(alt == 0, ref == 0), ("alt", precision)
             assert rel_max(alt, ref) <= tol, ("alt", precision, rel_max(alt, ref))
+
+
+@pytest.mark.parametrize("levels,r", [(1, 4), (2, 3), (3, 2), (4, 1), (2, 0), (1, 2)])
+def test_other_level_counts_and_radii(levels, r):
+    """num_levels and radius are runtime arguments of the reference API (corr.py:13); anything but (4, 3|4)
+    goes through the generic-stride kernels."""
+    import corr
+    B, D, H, W = 2, 24, 20, 36
+    gen = torch.Generator().manual_seed(levels * 10 + r)
+    f1 = torch.randn(B, D, H, W, generator=gen)
+    f2 = torch.randn(B, D, H, W, generator=gen)
+    c = coords_for("sigma4", B, H, W, gen)
+    ref = oracle.lookup(oracle.build_pyramid(f1, f2, levels), c.numpy(), r)
+    with torch.no_grad():
+        blk = corr.CorrBlock(f1.cuda(), f2.cuda(), num_levels=levels, radius=r, precision="fp32")
+        assert len(blk.corr_pyramid) == levels
+        out = blk(c.cuda()).cpu().numpy()
+        assert out.shape == (B, levels * (2 * r + 1) ** 2, H, W)
+        assert np.array_equal(out == 0, ref == 0) and rel_max(out, ref) <= 1e-5
+        alt = corr.AlternateCorrBlock(f1.cuda(), f2.cuda(), num_levels=levels, radius=r)(c.cuda()).cpu().numpy()
+        assert np.array_equal(alt == 0, ref == 0) and rel_max(alt, ref) <= 1e-2
+    # and with gradients
+    a, b = f1.cuda().requires_grad_(True), f2.cuda().requires_grad_(True)
+    out = corr.CorrBlock(a, b, num_levels=levels, radius=r, precision="fp32")(c.cuda())
+    out.sum().backward()
+    ra, rb = f1.clone().requires_grad_(True), f2.clone().requires_grad_(True)
+    from oracle import torch_restatement as tr
+    tr.TorchCorrBlock(ra, rb, levels, r)(c).sum().backward()
+    for got, want in ((a.grad, ra.grad), (b.grad, rb.grad)):
+        want = want.numpy()
+        assert np.allclose(got.cpu().numpy(), want, rtol=1e-3, atol=1e-4 * np.abs(want).max())
