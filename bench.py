@@ -160,7 +160,7 @@ def run_cpu_reference(steps: int, warmup: int, sample_pairs: int = 1):
                       "oracle/torch_restatement.py (same ATen ops as core/corr.py) inside harness/raft_stock.py"}
 
 
-def measure_other_configs(dev, hbm_peak_gbs):
+def measure_other_configs(dev, hbm_peak_gbs, model=None, frames=None):
     """Kernel-level numbers for the path's other BASELINE.json configurations (CUDA events, rank 0,
     N=1 only; a few hundred ms): configs[3] on-the-fly path at 1088x1920, configs[4] training-step
     correlation forward + backward.  Reported next to the headline, not part of it."""
@@ -217,6 +217,53 @@ def measure_other_configs(dev, hbm_peak_gbs):
 
     out["train_cfg5"] = {"workload": "CorrBlock build + 12 lookups, forward and backward, 368x496 (46x62 fmaps), batch 12",
                          "ms_per_step": timed(train_step, reps=3, warm=1)}
+    del f1, f2
+    # configs[2]: KITTI shape, 47x156 fmaps, batch 16, 24 iterations: the correlation path alone
+    B, D, H, W = 16, 256, 47, 156
+    f1 = torch.randn(B, D, H, W, device=dev, generator=gen)
+    f2 = torch.randn(B, D, H, W, device=dev, generator=gen)
+    c = grid(B, H, W) + 4 * torch.randn(B, 2, H, W, device=dev, generator=gen)
+
+    def kitti_path():
+        with torch.no_grad():
+            blk = raftcorr_dropin.CorrBlock(f1, f2)
+            for _ in range(24):
+                blk(c)
+
+    out["corr_path_cfg3"] = {"workload": "CorrBlock build + 24 lookups, KITTI 376x1248 (47x156 fmaps), batch 16",
+                             "ms_per_step": timed(kitti_path, reps=3, warm=1)}
+    del f1, f2
+    # the step after the path: convex upsampling at configs[1] size, this library against the reference's ops
+    import upsample as raftcorr_upsample
+    from oracle import torch_restatement as tr
+    B, H, W = BATCH_PER_GPU, IMG_H // 8, IMG_W // 8
+    masks = [torch.randn(B, 576, H, W, device=dev, generator=gen) for _ in range(4)]   # 4 x 130 MB > L2
+    flow = torch.randn(B, 2, H, W, device=dev, generator=gen)
+    turn = {"i": 0}
+
+    def next_mask():
+        turn["i"] += 1
+        return masks[turn["i"] & 3]
+
+    with torch.no_grad():
+        ours = timed(lambda: raftcorr_upsample.upsample_flow(flow, next_mask()), reps=20)
+        stock = timed(lambda: tr.upsample_flow(flow, next_mask()), reps=5)
+    up_bytes = B * H * W * (2304 + 8 + 512)
+    out["upsample_flow"] = {"workload": "RAFT.upsample_flow at 55x128, batch 8 (SURVEY.md 8f-4)", "us": ours * 1e3,
+                            "algorithmic_gb_s": up_bytes / ours / 1e6, "frac_hbm": up_bytes / ours / 1e6 / hbm_peak_gbs,
+                            "same_ops_as_reference_on_this_gpu_us": stock * 1e3}
+    del masks
+    # the reference's own op sequence on this GPU through stock PyTorch (ATen + cuBLAS; SURVEY.md 8d "additional
+    # honest baseline"): same model, same frames, only the correlation block and the upsampling differ
+    if model is not None and frames is not None:
+        def stock_step():
+            with torch.no_grad():
+                model(frames[0], frames[1], lambda a, b, r: tr.TorchCorrBlock(a, b, LEVELS, r), iters=ITERS)
+
+        ms = timed(stock_step, reps=3, warm=1)
+        out["reference_ops_on_this_gpu"] = {
+            "workload": "configs[1] with the reference's CorrBlock / upsample_flow op sequence (stock PyTorch) on the B200",
+            "ms_per_step": ms, "frame_pairs_per_s": BATCH_PER_GPU / (ms * 1e-3)}
     return out
 
 
@@ -437,7 +484,7 @@ def main():
         "clocks": clocks,
     }
     if n_gpus == 1:
-        line["other_configs"] = measure_other_configs(dev, peak)
+        line["other_configs"] = measure_other_configs(dev, peak, model, (dev1, dev2))
     if not args.skip_cpu_baseline and n_gpus == 1:
         ref = run_cpu_reference(steps=1, warmup=1)
         line["cpu_baseline"] = {"value": ref["value"], "unit": UNIT, "cores": ref["cores"], "kind": ref["kind"],
