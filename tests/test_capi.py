@@ -54,6 +54,12 @@ def test_bad_arguments_are_rejected_before_any_launch():
     assert lib.raftcorr_lookup_fwd(lv, 9, 16, 16, 1, 8, 8, 4, 0, None) == -1   # num_levels
     assert lib.raftcorr_build_pyramid(None, None, 1, 8, 8, 8, 4, lv, 1, None, 0, None) == -1
     assert lib.raftcorr_alt_fwd(None, None, None, None, 1, 8, 8, 8, 8, 8, 4, 2, 1.0, None) == -1
+    assert lib.raftcorr_upsample_flow_fwd(None, None, None, 1, 8, 8, None) == -1
+    assert b"NULL" in lib.raftcorr_last_error()
+    assert lib.raftcorr_upsample_flow_fwd(16, 16, 16, 1, 0, 8, None) == -1
+    assert lib.raftcorr_upsample_flow_bwd(16, 16, 16, None, None, 1, 8, 8, None) == -1
+    assert b"nothing to compute" in lib.raftcorr_last_error()
+    assert lib.raftcorr_upflow8(16, 8, 1, 8, 8, None) == -1    # output not 16-byte aligned
     assert lib.raftcorr_build_workspace_bytes(8, 256, 55, 128, _capi.PREC_BF16) == 2 * 8 * 7040 * 256 * 2
     # fp32-accurate mode: hi/lo tf32 splits of both fmaps for the tensor-core path; the CUDA-core
     # fallback (D not a multiple of 8) needs none
@@ -70,6 +76,11 @@ def test_python_boundary_refuses_cpu_tensors():
     f = torch.randn(1, 8, 16, 16)
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         corr.CorrBlock(f, f)
+    import upsample
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        upsample.upsample_flow(torch.zeros(1, 2, 4, 4), torch.zeros(1, 576, 4, 4))
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        upsample.upflow8(torch.zeros(1, 2, 4, 4))
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         alt_cuda_corr.forward(f.permute(0, 2, 3, 1).contiguous(), f.permute(0, 2, 3, 1).contiguous(),
                               torch.zeros(1, 1, 16, 16, 2), 4)
