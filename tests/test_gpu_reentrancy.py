@@ -69,3 +69,39 @@ def test_build_and_lookup_are_cuda_graph_capturable():
     g.replay()
     torch.cuda.synchronize()
     assert torch.allclose(out, 2.0 * eager, rtol=2e-2, atol=1e-3)
+
+
+def test_whole_refinement_loop_replays_as_one_cuda_graph():
+    """a full 12-iteration RAFT forward (stock encoders + this library's build, lookups and
+    upsampling) captured once and replayed gives the eager result; the on-the-fly block and upflow8 capture too."""
+    import corr
+    import upsample
+    from harness.raft_stock import StockRAFT
+    torch.manual_seed(11)
+    model = StockRAFT().eval().cuda()
+    gen = torch.Generator().manual_seed(2)
+    im1 = (torch.rand(1, 3, 192, 256, generator=gen) * 255).cuda()
+    im2 = (torch.rand(1, 3, 192, 256, generator=gen) * 255).cuda()
+
+    def run(factory):
+        with torch.no_grad():
+            lo, up = model(im1, im2, factory, iters=12, upsampler=upsample.upsample_flow)
+            return lo, up, upsample.upflow8(lo)
+
+    for factory in (lambda a, b, r: corr.CorrBlock(a, b, radius=r),
+                    lambda a, b, r: corr.AlternateCorrBlock(a, b, radius=r)):
+        eager = [t.clone() for t in run(factory)]       # also warms cuDNN and the one-time kernel set-up
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            run(factory)
+            with torch.cuda.graph(g, stream=side):
+                outs = run(factory)
+        torch.cuda.current_stream().wait_stream(side)
+        for t in outs:
+            t.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        for got, want in zip(outs, eager):
+            assert torch.allclose(got, want, rtol=1e-4, atol=1e-4), (got - want).abs().max().item()
