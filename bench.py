@@ -261,6 +261,27 @@ def measure_other_configs(dev, hbm_peak_gbs, model=None, frames=None):
                 model(frames[0], frames[1], lambda a, b, r: tr.TorchCorrBlock(a, b, LEVELS, r), iters=ITERS)
 
         ms = timed(stock_step, reps=3, warm=1)
+        # batch 1 (what evaluate.py / demo.py run): the loop is launch-bound, so the same forward is also timed as
+        # one CUDA graph replay (every kernel of this library is capturable)
+        one = (frames[0][:1].contiguous(), frames[1][:1].contiguous())
+        factory = lambda a, b, r: raftcorr_dropin.CorrBlock(a, b, num_levels=LEVELS, radius=r)  # noqa: E731
+
+        def b1_step():
+            with torch.no_grad():
+                return model(one[0], one[1], factory, iters=ITERS, upsampler=raftcorr_upsample.upsample_flow)[1]
+
+        eager_ms = timed(b1_step, reps=5, warm=2)
+        graph, side = torch.cuda.CUDAGraph(), torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            b1_step()
+            with torch.cuda.graph(graph, stream=side):
+                b1_step()
+        torch.cuda.current_stream().wait_stream(side)
+        graph_ms = timed(graph.replay, reps=10, warm=2)
+        out["latency_batch1"] = {"workload": "configs[1] shape at batch 1, 12 iterations", "eager_ms": eager_ms,
+                                 "cuda_graph_replay_ms": graph_ms}
+        del graph
         out["reference_ops_on_this_gpu"] = {
             "workload": "configs[1] with the reference's CorrBlock / upsample_flow op sequence (stock PyTorch) on the B200",
             "ms_per_step": ms, "frame_pairs_per_s": BATCH_PER_GPU / (ms * 1e-3)}
