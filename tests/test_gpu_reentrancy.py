@@ -105,3 +105,45 @@ def test_whole_refinement_loop_replays_as_one_cuda_graph():
         torch.cuda.synchronize()
         for got, want in zip(outs, eager):
             assert torch.allclose(got, want, rtol=1e-4, atol=1e-4), (got - want).abs().max().item()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_data_parallel_style_threads_on_two_devices():
+    """nn.DataParallel (train.py:138) calls the block from one thread per GPU: every entry point must work on
+    the tensors' device whatever the thread's current device is, with identical results on both devices."""
+    import corr
+    import upsample
+    gen = torch.Generator().manual_seed(21)
+    B, D, H, W = 2, 64, 24, 40
+    f1 = torch.randn(B, D, H, W, generator=gen)
+    f2 = torch.randn(B, D, H, W, generator=gen)
+    c = coords_for("sigma4", B, H, W, gen)
+    flow = torch.randn(B, 2, H, W, generator=gen)
+    mask = torch.randn(B, 576, H, W, generator=gen)
+    gout = torch.randn(B, 324, H, W, generator=gen)
+    results, errors = {}, []
+
+    def worker(dev, current):
+        try:
+            torch.cuda.set_device(current)          # deliberately not always the tensors' device
+            d = torch.device("cuda", dev)
+            a, b = f1.to(d).requires_grad_(True), f2.to(d).requires_grad_(True)
+            out = corr.CorrBlock(a, b)(c.to(d))
+            out.backward(gout.to(d))
+            with torch.no_grad():
+                alt = corr.AlternateCorrBlock(f1.to(d), f2.to(d))(c.to(d))
+                up = upsample.upsample_flow(flow.to(d), mask.to(d))
+            torch.cuda.synchronize(d)
+            results[dev] = [t.detach().cpu() for t in (out, a.grad, b.grad, alt, up)]
+        except Exception as exc:   # pragma: no cover
+            errors.append((dev, exc))
+
+    threads = [threading.Thread(target=worker, args=(0, 1)), threading.Thread(target=worker, args=(1, 0))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for x, y in zip(results[0], results[1]):
+        assert torch.allclose(x, y, rtol=1e-3, atol=1e-4 * y.abs().max().item())
+    assert torch.equal(results[0][0], results[1][0]) and torch.equal(results[0][4], results[1][4])
