@@ -44,3 +44,29 @@ def test_harness_matches_reference_model(small):
         for k in ("corr", "raft", "utils", "utils.utils", "update", "extractor"):
             sys.modules.pop(k, None)
         sys.modules.update(saved_mods)
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree not present")
+@pytest.mark.parametrize("alternate", [False, True])
+def test_unmodified_reference_model_picks_up_the_drop_in(alternate):
+    """with this repository's package directory ahead of core/ on sys.path, the reference's
+    own raft.py (unmodified) binds this library's CorrBlock / AlternateCorrBlock.  There is no GPU in the build
+    container, so the proof is that the forward reaches the drop-in and stops at its no-CPU-fallback check."""
+    import corr as dropin
+    names = ("corr", "raft", "utils", "utils.utils", "update", "extractor")
+    saved = list(sys.path)
+    saved_mods = {k: sys.modules.pop(k) for k in names if k in sys.modules}
+    sys.modules["corr"] = dropin               # what `sys.path.insert(0, "pytorch-raft_b200")` resolves to
+    sys.path.insert(1, REF)
+    try:
+        import raft
+        assert raft.CorrBlock is dropin.CorrBlock and raft.AlternateCorrBlock is dropin.AlternateCorrBlock
+        model = raft.RAFT(argparse.Namespace(small=False, mixed_precision=False, alternate_corr=alternate)).eval()
+        im = torch.rand(1, 3, 128, 160) * 255
+        with torch.no_grad(), pytest.raises(RuntimeError, match="CUDA tensor"):
+            model(im, im, iters=1, test_mode=True)
+    finally:
+        sys.path[:] = saved
+        for k in names:
+            sys.modules.pop(k, None)
+        sys.modules.update(saved_mods)
