@@ -310,9 +310,16 @@ lookup_bwd_kernel(const __grid_constant__ LookupBwdParams p) {
 
 }  // namespace
 
+int launch_lookup_bwd_tma(const raftcorr_level* glevels, int L, const float* coords, const float* gout, int B, int H,
+                          int W, int r, int mode, cudaStream_t stream);
+
 int launch_lookup_bwd(const raftcorr_level* levels, const raftcorr_level* glevels, int L,
                       const float* coords, const float* gout, float* gcoords, int B, int H, int W,
                       int r, int mode, cudaStream_t stream) {
+  if (glevels && !gcoords) {   // RAFT's case (coords are detached, core/raft.py:123): TMA reduce-add path
+    const int rc = launch_lookup_bwd_tma(glevels, L, coords, gout, B, H, W, r, mode, stream);
+    if (rc != 1) return rc;
+  }
   LookupBwdParams p;
   for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
     const int s = l < L ? l : 0;

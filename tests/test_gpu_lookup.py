@@ -178,3 +178,35 @@ def test_channels_last_output_is_the_same_tensor():
         b = ops.lookup(pyr, c, r, channels_last=True)
         assert b.shape == a.shape and b.is_contiguous(memory_format=torch.channels_last)
         assert torch.equal(a, b), (B, H, W, L, r)
+
+
+@pytest.mark.parametrize("r", [4, 3])
+@pytest.mark.parametrize("kind", ["grid", "half", "sigma4", "sigma30", "wild"])
+def test_backward_tma_reduce_path_equals_atomic_scatter(kind, r):
+    """d(pyramid) through TMA reduce-add boxes (the path RAFT takes: coords detached) against the atomic
+    scatter kernel (forced by also asking for d coords).  Same terms, so only the summation order differs;
+    'grid' has floor flips on ~8 % of its taps (irregular windows fall back per query), 'sigma30' pushes
+    windows across the border, 'wild' has NaN / inf / huge coordinates.  Padding columns stay untouched."""
+    B, H, W = 2, 30, 44
+    gen = torch.Generator().manual_seed(100 + r)
+    if kind == "wild":
+        c = coords_for("sigma4", B, H, W, gen)
+        c[0, 0, 3, 5], c[0, 1, 4, 6], c[1, 0, 7, 7], c[1, 1, 0, 0] = float("nan"), float("inf"), 3.0e38, -1.0e9
+        c[1, :, 10, 10] = torch.tensor([1.7e7, -2.5e7])
+    else:
+        c = coords_for(kind, B, H, W, gen)
+    c = c.cuda()
+    gout = torch.randn(B, 4 * (2 * r + 1) ** 2, H, W, generator=gen).cuda()
+    pyr = ops.Pyramid(B, H, W, 4, "cuda", zero=True)
+    ga = ops.Pyramid(B, H, W, 4, "cuda", zero=True)
+    gb = ops.Pyramid(B, H, W, 4, "cuda", zero=True)
+    for _ in range(2):      # two calls accumulate, like two refinement iterations
+        ops.lookup_backward(None, ga, c, gout, r, False)
+        ops.lookup_backward(pyr, gb, c, gout, r, True)
+    torch.cuda.synchronize()
+    for l in range(4):
+        a, b = ga.storage[l], gb.storage[l]
+        assert torch.isfinite(a).all()
+        scale = b.abs().max().item()
+        assert torch.allclose(a, b, rtol=1e-5, atol=1e-6 * max(scale, 1.0)), (l, (a - b).abs().max().item())
+        assert torch.equal(a[:, :, ga.desc[l].W:], torch.zeros_like(a[:, :, ga.desc[l].W:]))

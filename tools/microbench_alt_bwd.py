@@ -42,7 +42,7 @@ if which in ("all", "bwd"):
     gp = ops.Pyramid(B, H, W, 4, "cuda", zero=True)
     go = torch.randn(B, 324, H, W, device="cuda")
     ms = timeit(lambda: ops.lookup_backward(None, gp, c, go, 4, False), reps=5)
-    print(f"  lookup_bwd (scatter): {ms*1e3:.1f} us")
+    print(f"  lookup_bwd (TMA reduce-add boxes, incl. host call): {ms*1e3:.1f} us")
     ms = timeit(lambda: ops.build_backward(gp, f1.detach(), f2.detach()), reps=3)
     print(f"  build_bwd (unpool + 2 fp32 GEMMs): {ms:.2f} ms  {4*B*(H*W)**2*D/ms/1e9:.1f} TFLOP/s")
 if which in ("all", "altbwd"):
