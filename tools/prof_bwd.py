@@ -19,3 +19,7 @@ t1 = time.perf_counter()
 torch.cuda.synchronize()
 t2 = time.perf_counter()
 print(f"host issue {1e6*(t1-t0)/200:.1f} us/call, with drain {1e6*(t2-t0)/200:.1f} us/call")
+f1 = torch.randn(B, D, H, W, device="cuda"); f2 = torch.randn(B, D, H, W, device="cuda")
+for _ in range(2):
+    ops.build_backward(gp, f1, f2)
+torch.cuda.synchronize()
