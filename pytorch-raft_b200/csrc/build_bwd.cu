@@ -48,45 +48,67 @@ __device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
   lo = __uint_as_float(r);
 }
 
-// Tensor-core variant of the un-pool: a 32x32 (i, j) tile of dC, written as tf32 hi/lo splits both
+// Tensor-core variant of the un-pool: a 32 (i) x 128 (j) tile of dC, written as tf32 hi/lo splits both
 // as dC[i][j] (pitch Np) and transposed as dCT[j][i], so that both backward GEMMs see K-major operands.
+// Both copies leave as 16-byte stores (N is a multiple of 4 on this path, so is Np).
+constexpr int kUI = 32, kUJ = 128, kUPitch = kUJ + 1;   // odd pitch: conflict-free transposed reads
 __global__ void __launch_bounds__(256)
 unpool_split_kernel(const __grid_constant__ GradLevels g, float* __restrict__ c_hi, float* __restrict__ c_lo,
                     float* __restrict__ t_hi, float* __restrict__ t_lo, int N, int Np, int W, float inv_sqrtD) {
-  __shared__ float tile[32][33];
+  __shared__ float tile[kUI][kUPitch];
   const int b = blockIdx.z;
-  const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+  const int i0 = blockIdx.y * kUI, j0 = blockIdx.x * kUJ;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const long long base = (long long)b * N * Np;
-  for (int r = w; r < 32; r += 8) {
-    const int i = i0 + r, j = j0 + lane;
-    float v = 0.0f;
-    if (i < N && j < N) {
+  // phase 1: lane owns 4 consecutive j of one row i; pixel coordinates of the 4 are decoded once
+  const int j = j0 + 4 * lane;
+  int jy[4], jx[4];
+  {
+    const int y = j / W, x = j - y * W;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {   // the 4 columns may run over the end of an image row
+      const int over = (x + k) / W;
+      jy[k] = y + over;
+      jx[k] = (x + k) - over * W;
+    }
+  }
+  for (int r = w; r < kUI; r += 8) {
+    const int i = i0 + r;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (i < N && j < N) {     // N % 4 == 0 and j % 4 == 0: all four columns are in range together
       const long long q = (long long)b * N + i;
-      const int jy = j / W, jx = j - jy * W;
-      float acc = 0.0f, wgt = 1.0f;
+      float wgt = inv_sqrtD;
       for (int l = 0; l < g.L; ++l) {
-        const int yy = jy >> l, xx = jx >> l;
-        if (yy < g.H[l] && xx < g.W[l])
-          acc += wgt * __ldg(g.data[l] + q * g.istride[l] + (long long)yy * g.pitch[l] + xx);
+        const float* img = g.data[l] + q * g.istride[l];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int yy = jy[k] >> l, xx = jx[k] >> l;
+          if (yy < g.H[l] && xx < g.W[l]) v[k] = fmaf(wgt, __ldg(img + (long long)yy * g.pitch[l] + xx), v[k]);
+        }
         wgt *= 0.25f;
       }
-      v = acc * inv_sqrtD;
-      float hi, lo;
-      split_tf32(v, hi, lo);
-      c_hi[base + (long long)i * Np + j] = hi;
-      c_lo[base + (long long)i * Np + j] = lo;
+      float hi[4], lo[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) split_tf32(v[k], hi[k], lo[k]);
+      const long long o = base + (long long)i * Np + j;
+      __stcs(reinterpret_cast<float4*>(c_hi + o), make_float4(hi[0], hi[1], hi[2], hi[3]));
+      __stcs(reinterpret_cast<float4*>(c_lo + o), make_float4(lo[0], lo[1], lo[2], lo[3]));
     }
-    tile[r][lane] = v;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) tile[r][4 * lane + k] = v[k];
   }
   __syncthreads();
-  for (int r = w; r < 32; r += 8) {
-    const int j = j0 + r, i = i0 + lane;
-    if (i < N && j < N) {
-      float hi, lo;
-      split_tf32(tile[lane][r], hi, lo);
-      t_hi[base + (long long)j * Np + i] = hi;
-      t_lo[base + (long long)j * Np + i] = lo;
+  // phase 2: transposed rows dCT[j][i0 .. i0+31]; a lane writes 4 consecutive i of one j, a warp 4 rows
+  const int i4 = (lane & 7) * 4, jsub = lane >> 3;
+  for (int r = w * 4 + jsub; r < kUJ; r += 32) {
+    const int jj = j0 + r, i = i0 + i4;
+    if (jj < N && i < N) {     // i % 4 == 0 and N % 4 == 0: the four rows are in range together
+      float hi[4], lo[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) split_tf32(tile[i4 + k][r], hi[k], lo[k]);
+      const long long o = base + (long long)jj * Np + i;
+      __stcs(reinterpret_cast<float4*>(t_hi + o), make_float4(hi[0], hi[1], hi[2], hi[3]));
+      __stcs(reinterpret_cast<float4*>(t_lo + o), make_float4(lo[0], lo[1], lo[2], lo[3]));
     }
   }
 }
@@ -214,7 +236,7 @@ int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, cons
     float* f1_lo = reinterpret_cast<float*>(w + 4 * cn + fn);
     float* f2_hi = reinterpret_cast<float*>(w + 4 * cn + 2 * fn);
     float* f2_lo = reinterpret_cast<float*>(w + 4 * cn + 3 * fn);
-    dim3 ugrid((unsigned)((N + 31) / 32), (unsigned)((N + 31) / 32), (unsigned)B);
+    dim3 ugrid((unsigned)((N + kUJ - 1) / kUJ), (unsigned)((N + kUI - 1) / kUI), (unsigned)B);
     unpool_split_kernel<<<ugrid, 256, 0, stream>>>(g, c_hi, c_lo, t_hi, t_lo, (int)N, (int)Np, W, inv_sqrtD);
     RC_CHECK_CUDA(cudaGetLastError());
     split_rows_kernel<<<148 * 8, 256, 0, stream>>>(f1, f1_hi, f1_lo, (long long)B * D, (int)N, (int)Np);
