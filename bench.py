@@ -67,13 +67,16 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic_per_launch():
-    """dram read+write bytes per lookup launch from the committed ncu --set full capture."""
+def ncu_traffic_per_launch(channels_last: bool):
+    """dram read+write bytes per lookup launch from the committed ncu --set full capture of the kernel variant
+    this run uses (NCHW or channels-last output)."""
     path = os.path.join(ROOT, "profiles", "lookup_traffic.json")
     if os.path.exists(path):
         try:
             d = json.load(open(path))
             if d.get("workload") == "cfg2_b8_55x128":
+                if channels_last:
+                    return float(d["channels_last"]["dram_bytes_per_launch"]) if "channels_last" in d else None
                 return float(d["dram_bytes_per_launch"])
         except Exception:
             pass
@@ -296,6 +299,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=None, help="bf16 (default) | tf32 | fp32 for the volume build")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--stock-convc1", action="store_true",
+                    help="run convc1 + bias + ReLU (update.py:83,90) as stock torch ops on an NCHW lookup instead of "
+                         "the library's tensor-core 1x1 convolution on a channels-last lookup")
     ap.add_argument("--stock-upsample", action="store_true",
                     help="run RAFT.upsample_flow as the reference's torch op sequence instead of this library's kernel")
     ap.add_argument("--cudnn-benchmark", action="store_true", help="let cuDNN autotune the stock convolutions")
@@ -349,7 +355,8 @@ def main():
     host_flow = torch.empty(BATCH_PER_GPU, 2, IMG_H, IMG_W).pin_memory()
     factory = lambda f1, f2, r: raftcorr_dropin.CorrBlock(f1, f2, num_levels=LEVELS, radius=r,  # noqa: E731
                                                           precision=args.precision,
-                                                          channels_last=args.channels_last)
+                                                          channels_last=args.channels_last or not args.stock_convc1)
+    convc1_fn = None if args.stock_convc1 else raftcorr_dropin.conv1x1_relu
 
     lookup_events = []
 
@@ -373,7 +380,7 @@ def main():
 
     def step_resident(hook=None):
         with torch.no_grad():
-            return model(dev1, dev2, factory, iters=ITERS, lookup_hook=hook, upsampler=upsampler)[1]
+            return model(dev1, dev2, factory, iters=ITERS, lookup_hook=hook, upsampler=upsampler, convc1_fn=convc1_fn)[1]
 
     # End to end: every step copies its frames from pinned host memory and returns its flow to pinned host
     # memory.  The copies run on a second stream so that step i+1's frames travel while step i computes and
@@ -404,7 +411,8 @@ def main():
         prefetch_frames(slot ^ 1)
         with torch.no_grad():
             main.wait_event(ev_ready[slot])
-            flow = model(frame_slots[slot][0], frame_slots[slot][1], factory, iters=ITERS, upsampler=upsampler)[1]
+            flow = model(frame_slots[slot][0], frame_slots[slot][1], factory, iters=ITERS, upsampler=upsampler,
+                         convc1_fn=convc1_fn)[1]
             ev_free[slot].record(main)
             flow.record_stream(copy_stream)
             with torch.cuda.stream(copy_stream):
@@ -487,16 +495,20 @@ def main():
         "data": "synthetic",
         "config": dict(base_config, l2="inputs exceed L2 (2.1 GB pyramid + 115 MB frames per step)",
                        build_precision=args.precision or "bf16", encoders="stock PyTorch/cuDNN fp32",
+                       convc1="stock torch conv2d + relu on an NCHW lookup" if args.stock_convc1 else
+                       "raftcorr_conv1x1_nhwc_fwd (tf32 tcgen05, bias + ReLU epilogue) on a channels-last lookup",
                        upsample="stock torch ops (raft.py:72-83)" if args.stock_upsample else
                        "raftcorr_upsample_flow_fwd, every iteration like the reference",
                        memory_format="channels_last" if args.channels_last else "contiguous (NCHW, as the reference)"),
         "e2e": {"value": pairs / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
                 "copies": "pinned host <-> device on a second stream, double-buffered, overlapping the neighbouring steps"},
-        # pack + tcgen05 build + 12 lookups (+ 12 convex upsamplings) per step
-        "gpu_launches": (2 + ITERS * (1 if args.stock_upsample else 2)) * args.steps * n_gpus,
-        "roofline": {"kernel": "lookup_fwd_tma_kernel", "bound": "hbm", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic_per_launch(),
+        # pack + tcgen05 build + 12 lookups (+ 12 tensor-core 1x1 convolutions, + 12 convex upsamplings) per step
+        "gpu_launches": (2 + ITERS * (1 + (not args.stock_upsample) + (not args.stock_convc1))) * args.steps * n_gpus,
+        "roofline": {"kernel": "lookup_fwd_tma_kernel" + ("" if args.stock_convc1 and not args.channels_last
+                                                          else " (channels-last output)"),
+                     "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": ncu_traffic_per_launch(args.channels_last or not args.stock_convc1),
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": queries * LOOKUP_BYTES_PER_QUERY,
                      "launch_us": lookup_avg_ms * 1e3, "launches_timed": len(lookup_ms)},
         "kernels": {"lookup_us": lookup_avg_ms * 1e3, "build_ms": build_ms,

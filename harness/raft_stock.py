@@ -125,8 +125,8 @@ class SmallMotionEncoder(nn.Module):
         self.convf2 = nn.Conv2d(64, 32, 3, padding=1)
         self.conv = nn.Conv2d(128, 80, 3, padding=1)
 
-    def forward(self, flow, corr):
-        c = F.relu(self.convc1(corr))
+    def forward(self, flow, corr, encoded=False):
+        c = corr if encoded else F.relu(self.convc1(corr))
         f = F.relu(self.convf2(F.relu(self.convf1(flow))))
         return torch.cat([F.relu(self.conv(torch.cat([c, f], dim=1))), flow], dim=1)
 
@@ -155,8 +155,8 @@ class SmallUpdateBlock(nn.Module):
         self.gru = GRU3x3(hidden, 82 + 64)
         self.flow_head = FlowHead(hidden, 128)
 
-    def forward(self, net, inp, corr, flow):
-        net = self.gru(net, torch.cat([inp, self.encoder(flow, corr)], dim=1))
+    def forward(self, net, inp, corr, flow, encoded=False):
+        net = self.gru(net, torch.cat([inp, self.encoder(flow, corr, encoded)], dim=1))
         return net, None, self.flow_head(net)
 
 
@@ -171,8 +171,9 @@ class MotionEncoder(nn.Module):
         self.convf2 = nn.Conv2d(128, 64, 3, padding=1)
         self.conv = nn.Conv2d(256, 126, 3, padding=1)
 
-    def forward(self, flow, corr):
-        c = F.relu(self.convc2(F.relu(self.convc1(corr))))
+    def forward(self, flow, corr, encoded=False):
+        """``encoded``: ``corr`` already is relu(convc1(lookup)) (the fused lookup of the library)."""
+        c = F.relu(self.convc2(corr if encoded else F.relu(self.convc1(corr))))
         f = F.relu(self.convf2(F.relu(self.convf1(flow))))
         return torch.cat([F.relu(self.conv(torch.cat([c, f], dim=1))), flow], dim=1)
 
@@ -218,8 +219,8 @@ class UpdateBlock(nn.Module):
         self.mask = nn.Sequential(nn.Conv2d(128, 256, 3, padding=1), nn.ReLU(inplace=True),
                                   nn.Conv2d(256, 64 * 9, 1))
 
-    def forward(self, net, inp, corr, flow):
-        net = self.gru(net, torch.cat([inp, self.encoder(flow, corr)], dim=1))
+    def forward(self, net, inp, corr, flow, encoded=False):
+        net = self.gru(net, torch.cat([inp, self.encoder(flow, corr, encoded)], dim=1))
         return net, 0.25 * self.mask(net), self.flow_head(net)
 
 
@@ -272,11 +273,11 @@ class StockRAFT(nn.Module):
         return fmap1.float(), fmap2.float(), torch.tanh(net), torch.relu(inp)
 
     def forward(self, image1, image2, corr_factory, iters: int = 12, flow_init=None, lookup_hook=None,
-                upsampler=None, upsampler8=None):
+                upsampler=None, upsampler8=None, convc1_fn=None):
         """Returns (flow at 1/8 resolution, upsampled flow) like raft.py's test_mode.  ``upsampler(flow, mask)``
         replaces raft.py:72-83 (default: the stock-torch op sequence); like the reference it runs after
         every iteration (raft.py:134-139)."""
-        upsampler = upsampler or convex_upsample
+        upsampler = upsampler or convex_upsample   # ``convc1_fn``: see the loop below
         upsampler8 = upsampler8 or bilinear_upsample8
         fmap1, fmap2, net, inp = self.features(image1, image2)
         corr_fn = corr_factory(fmap1, fmap2, self.radius)
@@ -287,7 +288,12 @@ class StockRAFT(nn.Module):
         for _ in range(iters):
             coords1 = coords1.detach()
             corr = corr_fn(coords1) if lookup_hook is None else lookup_hook(corr_fn, coords1)
-            net, up_mask, delta = self.update_block(net, inp, corr, coords1 - coords0)
+            if convc1_fn is not None:
+                # ``convc1_fn(lookup, weight, bias)`` = relu(convc1(lookup)): the library's tensor-core 1x1
+                # convolution over a channels-last lookup instead of update.py:83,90
+                c1 = self.update_block.encoder.convc1
+                corr = convc1_fn(corr, c1.weight, c1.bias)
+            net, up_mask, delta = self.update_block(net, inp, corr, coords1 - coords0, convc1_fn is not None)
             coords1 = coords1 + delta
             flow = coords1 - coords0
             flow_up = upsampler8(flow) if up_mask is None else upsampler(flow, up_mask)

@@ -167,6 +167,26 @@ int raftcorr_upsample_flow_bwd(const float* flow, const float* mask, const float
  * (the small model's upsampling, raft.py:134-135).  flow (B,2,H,W) -> up (B,2,8H,8W). */
 int raftcorr_upflow8(const float* flow, float* up, int B, int H, int W, void* stream);
 
+/* ---- (5) lookup + the 1x1 convolution that consumes it: replaces
+ *      CorrBlock.__call__ (core/corr.py:29-50) followed by BasicMotionEncoder.convc1 + ReLU
+ *      (core/update.py:83,90; SmallMotionEncoder: update.py:66,72).  The samples are written once,
+ *      query-major, into `workspace` and consumed by a tf32 tcgen05 GEMM whose epilogue adds the bias,
+ *      applies the ReLU and stores NCHW — no 324-channel NCHW tensor, no layout shuffles, no separate
+ *      bias / ReLU passes.  weight: (out_channels, L*(2r+1)^2) row-major = the convolution's
+ *      (out_channels, C, 1, 1) weight; bias: (out_channels) or NULL; out: (B, out_channels, H, W).
+ *      TF32 products (what cuDNN uses for this convolution by default), fp32 accumulation.
+ *      Needs C % 4 == 0 and H*W % 4 == 0, else RAFTCORR_E_UNSUPPORTED. */
+int64_t raftcorr_lookup_conv1x1_workspace_bytes(int B, int H, int W, int num_levels, int radius);
+/* The convolution half on its own, for a caller that already holds the channels-last lookup
+ * (raftcorr_lookup_fwd_nhwc): act (B, pixels, in_channels) -> out (B, out_channels, pixels),
+ * out = act . weight^T + bias, optional ReLU. */
+int raftcorr_conv1x1_nhwc_fwd(const float* act, const float* weight, const float* bias, float* out, int B,
+                              int pixels, int in_channels, int out_channels, int relu, void* stream);
+int raftcorr_lookup_conv1x1_fwd(const raftcorr_level* levels, int num_levels, const float* coords,
+                                const float* weight, const float* bias, float* out, int B, int H, int W,
+                                int radius, int coord_mode, int out_channels, int relu, void* workspace,
+                                int64_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

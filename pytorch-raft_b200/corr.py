@@ -56,12 +56,31 @@ class CorrBlock:
             return ops.LookupFn.apply(coords, token, self._holder, self.radius, self._coord_mode)
         return ops.lookup(self._holder["pyr"], coords, self.radius, self._coord_mode, self._channels_last)
 
+    def lookup_conv1x1(self, coords, weight, bias=None, relu=True):
+        """Extra: ``relu(conv1x1(self(coords)))`` — the lookup fused with the first layer of the
+        motion encoder (``convc1``, core/update.py:83,90) — without ever forming the (B, 324, H, W) tensor.
+        ``weight`` is the convolution's (out_channels, 324, 1, 1) weight.  TF32 products; inference only."""
+        if torch.is_grad_enabled() and (coords.requires_grad or weight.requires_grad or
+                                        (self._token is not None and self._token.requires_grad)):
+            raise RuntimeError("lookup_conv1x1 is an inference path: call the block and the convolution separately "
+                               "when gradients are needed")
+        return ops.lookup_conv1x1(self._holder["pyr"], coords, self.radius, weight, bias, relu, self._coord_mode)
+
     @staticmethod
     def corr(fmap1, fmap2, *, precision=None):
         """core/corr.py:52-60: the all-pairs volume (B,H,W,1,H,W), scaled by 1/sqrt(D)."""
         B, D, H, W = fmap1.shape
         pyr = ops.build_pyramid(fmap1, fmap2, 1, precision)
         return pyr.views()[0].reshape(B, H, W, 1, H, W)
+
+
+def conv1x1_relu(lookup, weight, bias=None):
+    """``relu(conv2d(lookup, weight, bias))`` for the 1x1 convolution that consumes the lookup
+    (BasicMotionEncoder.convc1, core/update.py:83,90) on the tensor cores, reading a lookup emitted with
+    ``CorrBlock(..., channels_last=True)`` in place (any other layout is converted first).  Inference only."""
+    if torch.is_grad_enabled() and (lookup.requires_grad or weight.requires_grad):
+        raise RuntimeError("conv1x1_relu is an inference path")
+    return ops.conv1x1_channels_last(lookup, weight, bias, relu=True)
 
 
 class AlternateCorrBlock:

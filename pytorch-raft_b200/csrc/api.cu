@@ -54,6 +54,10 @@ int launch_upsample_fwd(const float* flow, const float* mask, float* up, int B, 
 int launch_upsample_bwd(const float* flow, const float* mask, const float* gup, float* gflow, float* gmask, int B,
                         int H, int W, cudaStream_t stream);
 int launch_upflow8(const float* flow, float* up, int B, int H, int W, cudaStream_t stream);
+int launch_tc_conv1x1(const float* weight, long long w_pitch, const float* act, long long act_pitch,
+                      long long act_bstride, float* out, long long o_pitch, long long o_bstride, int B, int M, int Nn,
+                      int K, const float* bias, int relu, cudaStream_t stream);
+bool tc_gemm_available();
 int launch_alt_bwd(const float* f1, const float* f2, const float* coords, const float* gcorr,
                    float* g1, float* g2, float* gcoords, int B, int H1, int W1, int H2, int W2, int C,
                    int r, int mode, float scale, cudaStream_t stream);
@@ -267,6 +271,55 @@ int raftcorr_upflow8(const float* flow, float* up, int B, int H, int W, void* st
   RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "upflow8: bad sizes B=%d H=%d W=%d", B, H, W);
   RC_REQUIRE(!(reinterpret_cast<uintptr_t>(up) & 15), "upflow8: up must be 16-byte aligned");
   return launch_upflow8(flow, up, B, H, W, (cudaStream_t)stream);
+}
+
+int64_t raftcorr_lookup_conv1x1_workspace_bytes(int B, int H, int W, int num_levels, int radius) {
+  if (B < 0 || H < 1 || W < 1 || num_levels < 1 || num_levels > RAFTCORR_MAX_LEVELS || radius < 0 || radius > 4)
+    return RAFTCORR_E_INVALID;
+  const int64_t rd = 2 * radius + 1;
+  return (int64_t)B * H * W * num_levels * rd * rd * (int64_t)sizeof(float);
+}
+
+int raftcorr_conv1x1_nhwc_fwd(const float* act, const float* weight, const float* bias, float* out, int B,
+                              int pixels, int in_channels, int out_channels, int relu, void* stream) {
+  RC_REQUIRE(act && weight && out, "conv1x1_nhwc_fwd: act/weight/out is NULL");
+  RC_REQUIRE(B >= 0 && pixels >= 1 && in_channels >= 1 && out_channels >= 1, "conv1x1_nhwc_fwd: bad sizes");
+  if ((in_channels & 3) || (pixels & 3) || !tc_gemm_available() || (reinterpret_cast<uintptr_t>(weight) & 15) ||
+      (reinterpret_cast<uintptr_t>(act) & 15) || (reinterpret_cast<uintptr_t>(out) & 15))
+    return raftcorr::fail(RAFTCORR_E_UNSUPPORTED,
+                          "conv1x1_nhwc_fwd: needs in_channels %% 4 == 0 and pixels %% 4 == 0 (%d, %d) and 16-byte "
+                          "aligned pointers", in_channels, pixels);
+  return launch_tc_conv1x1(weight, in_channels, act, in_channels, (long long)pixels * in_channels, out, pixels,
+                           (long long)out_channels * pixels, B, out_channels, pixels, in_channels, bias, relu,
+                           (cudaStream_t)stream);
+}
+
+int raftcorr_lookup_conv1x1_fwd(const raftcorr_level* levels, int num_levels, const float* coords,
+                                const float* weight, const float* bias, float* out, int B, int H, int W,
+                                int radius, int coord_mode, int out_channels, int relu, void* workspace,
+                                int64_t workspace_bytes, void* stream) {
+  RC_REQUIRE(coords && weight && out, "lookup_conv1x1_fwd: coords/weight/out is NULL");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "lookup_conv1x1_fwd: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(radius >= 0 && radius <= 4, "lookup_conv1x1_fwd: radius=%d not in [0,4]", radius);
+  RC_REQUIRE(valid_mode(coord_mode), "lookup_conv1x1_fwd: coord_mode=%d", coord_mode);
+  RC_REQUIRE(out_channels >= 1, "lookup_conv1x1_fwd: out_channels=%d", out_channels);
+  if (int rc = check_levels(levels, num_levels, H, W, "lookup_conv1x1_fwd")) return rc;
+  const int rd = 2 * radius + 1, C = num_levels * rd * rd;
+  const long long N = (long long)H * W;
+  if ((C & 3) || (N & 3) || !tc_gemm_available() || (reinterpret_cast<uintptr_t>(weight) & 15) ||
+      (reinterpret_cast<uintptr_t>(out) & 15))
+    return raftcorr::fail(RAFTCORR_E_UNSUPPORTED,
+                          "lookup_conv1x1_fwd: needs L*(2r+1)^2 %% 4 == 0 and H*W %% 4 == 0 (C=%d, H*W=%lld) and "
+                          "16-byte aligned weight/out", C, N);
+  const int64_t need = raftcorr_lookup_conv1x1_workspace_bytes(B, H, W, num_levels, radius);
+  if (!workspace || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 15))
+    return raftcorr::fail(RAFTCORR_E_WORKSPACE, "lookup_conv1x1_fwd: workspace %lld B < %lld B (or not 16-byte aligned)",
+                          (long long)workspace_bytes, (long long)need);
+  float* samples = static_cast<float*>(workspace);   // (B, H, W, C): every query's C samples contiguous
+  if (int rc = launch_lookup_fwd(levels, num_levels, coords, samples, B, H, W, radius, coord_mode, 1,
+                                 (cudaStream_t)stream))
+    return rc;
+  return raftcorr_conv1x1_nhwc_fwd(samples, weight, bias, out, B, (int)N, C, out_channels, relu, stream);
 }
 
 }  // extern "C"

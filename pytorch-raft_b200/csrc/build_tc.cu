@@ -50,6 +50,10 @@ struct BuildTcParams {
   uint32_t idesc;
   float inv_scale;    // 1 / sqrt(D)
   int Hl[RAFTCORR_MAX_LEVELS], Wl[RAFTCORR_MAX_LEVELS];
+  // plain epilogue extras (1x1-convolution use): per-row bias, ReLU, A shared by all batches
+  const float* bias;
+  int relu;
+  int a_batch_mul;    // 1: A has a batch dimension; 0: one A for every batch
 };
 
 // Stage one row segment (kNF floats per query, 32 queries) in swizzled shared memory and hand it
@@ -149,7 +153,7 @@ build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
             mbar_wait(empty_bar(s), ph ^ 1);
             mbar_expect_tx(full_bar(s), kStageBytes);
             const uint32_t a_dst = smem_base + s * kStageBytes;
-            tma_load_3d(a_dst, &ops.a[pass], full_bar(s), kb * p.k_elems, mt * kBlockM, b);
+            tma_load_3d(a_dst, &ops.a[pass], full_bar(s), kb * p.k_elems, mt * kBlockM, b * p.a_batch_mul);
             tma_load_4d(a_dst + kBytesA, &ops.b[pass], full_bar(s), kb * p.k_elems, tx * bx, ty * by, b);
           }
       }
@@ -211,8 +215,12 @@ build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
             if (lane == 0) mbar_arrive(tempty_bar(group));
           }
           if (!rows_live) continue;
+          const float bias = p.bias ? __ldg(p.bias + min(q0 + lane, p.N - 1)) : 0.0f;
 #pragma unroll
-          for (int c = 0; c < 32; ++c) f[c] *= p.inv_scale;
+          for (int c = 0; c < 32; ++c) {
+            f[c] = fmaf(f[c], p.inv_scale, bias);
+            if (p.relu) f[c] = f[c] < 0.0f ? 0.0f : f[c];   // NaN stays NaN, as in torch.relu
+          }
           const int n0 = tx * kBlockN + cc * 32;
           if (n0 < p.W) stage_and_store<32>(f, &mapL0, buf_base, nstores, lane, n0, 0, q0, b);
         }
@@ -504,6 +512,9 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   p.k_blocks = (int)((D + k_elems - 1) / k_elems);
   p.passes = passes;
   p.plain = 0;
+  p.bias = nullptr;
+  p.relu = 0;
+  p.a_batch_mul = 1;
   p.idesc = make_idesc(tf32);
   p.inv_scale = 1.0f / sqrtf((float)D);
   for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
@@ -517,22 +528,25 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
 //   C[b][m][n] = sum_k A[b][m][k] * B[b][n][k]      A = a_hi + a_lo, B = b_hi + b_lo (tf32 values)
 // All operands are K-major fp32 with row pitches / batch strides in elements; pitches and o_pitch
 // must be multiples of 4 (16-byte TMA strides).  K and N tails are zero-filled / clipped by TMA.
-int launch_tc_gemm_split(const float* a_hi, const float* a_lo, long long a_pitch, long long a_bstride,
-                         const float* b_hi, const float* b_lo, long long b_pitch, long long b_bstride,
-                         float* out, long long o_pitch, long long o_bstride, int B, int M, int Nn, int K,
-                         cudaStream_t stream) {
+namespace {
+// passes = 3: a_src/b_src = {hi, hi, lo} / {hi, lo, hi}; passes = 1: one tf32 pass over a_src[0] . b_src[0]^T.
+// a_bstride == 0 means one A for all batches.  bias (per row of C) and relu are applied in the epilogue.
+int launch_tc_gemm_any(const float* const* a_src, const float* const* b_src, int passes, long long a_pitch,
+                       long long a_bstride, long long b_pitch, long long b_bstride, float* out, long long o_pitch,
+                       long long o_bstride, int B, int M, int Nn, int K, const float* bias, int relu,
+                       cudaStream_t stream) {
   if (B == 0 || M == 0 || Nn == 0) return 0;
   if ((a_pitch | b_pitch | o_pitch | a_bstride | b_bstride | o_bstride) & 3)
     return fail(RAFTCORR_E_UNSUPPORTED, "tc_gemm: pitches must be multiples of 4 elements");
   TcOperandMaps ops;
-  const float* a_src[3] = {a_hi, a_hi, a_lo};
-  const float* b_src[3] = {b_hi, b_lo, b_hi};
+  const bool a_shared = a_bstride == 0;
   for (int ps = 0; ps < 3; ++ps) {
+    const int src = ps < passes ? ps : 0;
     {
-      cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)M, (cuuint64_t)B};
-      cuuint64_t strides[2] = {(cuuint64_t)a_pitch * 4, (cuuint64_t)a_bstride * 4};
+      cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)M, (cuuint64_t)(a_shared ? 1 : B)};
+      cuuint64_t strides[2] = {(cuuint64_t)a_pitch * 4, (cuuint64_t)(a_shared ? (long long)M * a_pitch : a_bstride) * 4};
       cuuint32_t box[3] = {32, kBlockM, 1};
-      if (int rc = encode(&ops.a[ps], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(a_src[ps]), dims, strides,
+      if (int rc = encode(&ops.a[ps], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(a_src[src]), dims, strides,
                           box, CU_TENSOR_MAP_SWIZZLE_128B, "gemm A"))
         return rc;
     }
@@ -540,7 +554,7 @@ int launch_tc_gemm_split(const float* a_hi, const float* a_lo, long long a_pitch
       cuuint64_t dims[4] = {(cuuint64_t)K, (cuuint64_t)Nn, 1, (cuuint64_t)B};
       cuuint64_t strides[3] = {(cuuint64_t)b_pitch * 4, (cuuint64_t)b_bstride * 4, (cuuint64_t)b_bstride * 4};
       cuuint32_t box[4] = {32, kBlockN, 1, 1};
-      if (int rc = encode(&ops.b[ps], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(b_src[ps]), dims, strides,
+      if (int rc = encode(&ops.b[ps], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(b_src[src]), dims, strides,
                           box, CU_TENSOR_MAP_SWIZZLE_128B, "gemm B"))
         return rc;
     }
@@ -566,15 +580,40 @@ int launch_tc_gemm_split(const float* a_hi, const float* a_lo, long long a_pitch
   p.tiles_x = (Nn + kBlockN - 1) / kBlockN;
   p.k_elems = 32;
   p.k_blocks = (K + 31) / 32;
-  p.passes = 3;
+  p.passes = passes;
   p.plain = 1;
   p.idesc = make_idesc(true);
   p.inv_scale = 1.0f;
+  p.bias = bias;
+  p.relu = relu;
+  p.a_batch_mul = a_shared ? 0 : 1;
   for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
     p.Hl[l] = 1;
     p.Wl[l] = Nn;
   }
   return launch_tc_kernel(true, ops, outm, p, stream);
+}
+}  // namespace
+
+int launch_tc_gemm_split(const float* a_hi, const float* a_lo, long long a_pitch, long long a_bstride,
+                         const float* b_hi, const float* b_lo, long long b_pitch, long long b_bstride,
+                         float* out, long long o_pitch, long long o_bstride, int B, int M, int Nn, int K,
+                         cudaStream_t stream) {
+  const float* a_src[3] = {a_hi, a_hi, a_lo};
+  const float* b_src[3] = {b_hi, b_lo, b_hi};
+  return launch_tc_gemm_any(a_src, b_src, 3, a_pitch, a_bstride, b_pitch, b_bstride, out, o_pitch, o_bstride, B, M, Nn,
+                            K, nullptr, 0, stream);
+}
+
+// One tf32 pass, C[b][m][n] = act(sum_k A[m][k] * B[b][n][k] + bias[m]) with A shared by all batches: a 1x1
+// convolution over NHWC activations whose result lands in NCHW (m = output channel, n = pixel).
+int launch_tc_conv1x1(const float* weight, long long w_pitch, const float* act, long long act_pitch,
+                      long long act_bstride, float* out, long long o_pitch, long long o_bstride, int B, int M, int Nn,
+                      int K, const float* bias, int relu, cudaStream_t stream) {
+  const float* a_src[3] = {weight, weight, weight};
+  const float* b_src[3] = {act, act, act};
+  return launch_tc_gemm_any(a_src, b_src, 1, w_pitch, 0, act_pitch, act_bstride, out, o_pitch, o_bstride, B, M, Nn, K,
+                            bias, relu, stream);
 }
 
 bool tc_gemm_available() { return get_encode() != nullptr; }

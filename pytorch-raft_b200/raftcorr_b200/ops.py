@@ -328,6 +328,60 @@ class AltFusedFn(torch.autograd.Function):
         return (gc_total.contiguous() if want_coords else None, g1_total, None, None, None, None, *g2)
 
 
+def lookup_conv1x1(pyr: Pyramid, coords: torch.Tensor, radius: int, weight: torch.Tensor,
+                   bias: Optional[torch.Tensor] = None, relu: bool = True, coord_mode=None) -> torch.Tensor:
+    """Window lookup followed by the 1x1 convolution (+ bias, + ReLU) that consumes it (update.py:83,90):
+    (B,2,H,W) coords -> (B, out_channels, H, W), TF32 products.  Inference only."""
+    _require_cuda_f32(coords, "coords")
+    _require_cuda_f32(weight, "weight")
+    coords = coords.contiguous()
+    B, _, H, W = coords.shape
+    rd = 2 * radius + 1
+    C = pyr.num_levels * rd * rd
+    cout = weight.shape[0]
+    if weight.numel() != cout * C:
+        raise RuntimeError(f"weight must hold (out_channels, {C}) values, got {tuple(weight.shape)}")
+    weight = weight.reshape(cout, C).contiguous()
+    if bias is not None:
+        _require_cuda_f32(bias, "bias")
+        bias = bias.contiguous()
+    out = torch.empty((B, cout, H, W), dtype=torch.float32, device=coords.device)
+    need = _capi.lib().raftcorr_lookup_conv1x1_workspace_bytes(B, H, W, pyr.num_levels, radius)
+    ws = torch.empty(max(int(need), 16) // 4, dtype=torch.float32, device=coords.device)
+    with _on_device(coords.device):
+        _capi.check(_capi.lib().raftcorr_lookup_conv1x1_fwd(
+            pyr.desc, pyr.num_levels, coords.data_ptr(), weight.data_ptr(),
+            bias.data_ptr() if bias is not None else None, out.data_ptr(), B, H, W, radius,
+            resolve_coord_mode(coord_mode), cout, 1 if relu else 0, ws.data_ptr(), ws.numel() * 4, _stream(coords)),
+            "raftcorr_lookup_conv1x1_fwd")
+    return out
+
+
+def conv1x1_channels_last(act: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None,
+                          relu: bool = True) -> torch.Tensor:
+    """relu(conv1x1(act)) for a (B, C, H, W) tensor held in channels_last memory (what ``lookup(...,
+    channels_last=True)`` returns) -> (B, out_channels, H, W) contiguous.  tcgen05 TF32 GEMM with the bias
+    and the ReLU in its epilogue.  Inference only."""
+    _require_cuda_f32(act, "act")
+    _require_cuda_f32(weight, "weight")
+    B, C, H, W = act.shape
+    if not act.is_contiguous(memory_format=torch.channels_last):
+        act = act.contiguous(memory_format=torch.channels_last)
+    cout = weight.shape[0]
+    if weight.numel() != cout * C:
+        raise RuntimeError(f"weight must hold (out_channels, {C}) values, got {tuple(weight.shape)}")
+    weight = weight.reshape(cout, C).contiguous()
+    if bias is not None:
+        _require_cuda_f32(bias, "bias")
+        bias = bias.contiguous()
+    out = torch.empty((B, cout, H, W), dtype=torch.float32, device=act.device)
+    with _on_device(act.device):
+        _capi.check(_capi.lib().raftcorr_conv1x1_nhwc_fwd(
+            act.data_ptr(), weight.data_ptr(), bias.data_ptr() if bias is not None else None, out.data_ptr(), B,
+            H * W, C, cout, 1 if relu else 0, _stream(act)), "raftcorr_conv1x1_nhwc_fwd")
+    return out
+
+
 # ---- the step after the path: flow upsampling (SURVEY.md §8f-4) ------------------------------------
 
 def _check_flow_mask(flow: torch.Tensor, mask: Optional[torch.Tensor]):

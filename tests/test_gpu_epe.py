@@ -43,6 +43,12 @@ def test_twelve_iteration_flow_epe(shape):
                        upsampler=upsample.upsample_flow)
     epe = (up - up_ref).pow(2).sum(1).sqrt().mean().item()
     assert epe <= 0.01, ("upsample", epe)
+    # ... and with convc1 (+ bias + ReLU) as the library's tensor-core GEMM over a channels-last lookup
+    with torch.no_grad():
+        lo, up = model(im1, im2, lambda a, b, r: corr.CorrBlock(a, b, radius=r, channels_last=True), iters=12,
+                       upsampler=upsample.upsample_flow, convc1_fn=corr.conv1x1_relu)
+    epe = (up - up_ref).pow(2).sum(1).sqrt().mean().item()
+    assert epe <= 0.01, ("conv1x1", epe)
     # the memory-lean block computes the same flow
     lo, up = _flows(model, im1[:1], im2[:1], lambda a, b, r: corr.AlternateCorrBlock(a, b, radius=r))
     epe = (up - up_ref[:1]).pow(2).sum(1).sqrt().mean().item()
