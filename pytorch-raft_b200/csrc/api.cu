@@ -58,6 +58,8 @@ int launch_tc_conv1x1(const float* weight, long long w_pitch, const float* act, 
                       long long act_bstride, float* out, long long o_pitch, long long o_bstride, int B, int M, int Nn,
                       int K, const float* bias, int relu, cudaStream_t stream);
 bool tc_gemm_available();
+int launch_conv1x1_tc(const float* weight, const float* act, float* out, int B, int M, int Nn, int K,
+                      const float* bias, int relu, cudaStream_t stream);
 int launch_alt_bwd(const float* f1, const float* f2, const float* coords, const float* gcorr,
                    float* g1, float* g2, float* gcoords, int B, int H1, int W1, int H2, int W2, int C,
                    int r, int mode, float scale, cudaStream_t stream);
@@ -289,6 +291,10 @@ int raftcorr_conv1x1_nhwc_fwd(const float* act, const float* weight, const float
     return raftcorr::fail(RAFTCORR_E_UNSUPPORTED,
                           "conv1x1_nhwc_fwd: needs in_channels %% 4 == 0 and pixels %% 4 == 0 (%d, %d) and 16-byte "
                           "aligned pointers", in_channels, pixels);
+  // all output channels x 128 pixels per tile when there are at most 256 output channels (csrc/conv1x1_tc.cu)
+  const int rc = launch_conv1x1_tc(weight, act, out, B, out_channels, pixels, in_channels, bias, relu,
+                                   (cudaStream_t)stream);
+  if (rc != 1) return rc;
   return launch_tc_conv1x1(weight, in_channels, act, in_channels, (long long)pixels * in_channels, out, pixels,
                            (long long)out_channels * pixels, B, out_channels, pixels, in_channels, bias, relu,
                            (cudaStream_t)stream);

@@ -24,7 +24,7 @@ def _exact_conv(x, w, b):
             torch.backends.cuda.matmul.allow_tf32 = old
 
 
-@pytest.mark.parametrize("B,H,W,r,cout", [(2, 24, 40, 4, 256), (1, 46, 62, 4, 256), (2, 23, 44, 3, 96), (1, 16, 20, 4, 40)])
+@pytest.mark.parametrize("B,H,W,r,cout", [(2, 24, 40, 4, 256), (1, 46, 62, 4, 256), (2, 23, 44, 3, 96), (1, 16, 20, 4, 40), (1, 16, 20, 4, 320)])
 def test_conv1x1_of_the_lookup_matches_torch(B, H, W, r, cout):
     import corr
     gen = torch.Generator().manual_seed(B * 100 + H)
