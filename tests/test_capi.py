@@ -84,3 +84,29 @@ def test_python_boundary_refuses_cpu_tensors():
     with pytest.raises(RuntimeError, match="CUDA tensor"):
         alt_cuda_corr.forward(f.permute(0, 2, 3, 1).contiguous(), f.permute(0, 2, 3, 1).contiguous(),
                               torch.zeros(1, 1, 16, 16, 2), 4)
+
+
+def test_header_is_plain_c(tmp_path):
+    """The boundary is a C ABI: include/raftcorr.h must compile as C99 on its own and a C program must link
+    against the library using nothing but that header."""
+    import shutil
+    import subprocess
+    gcc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no C compiler")
+    header = os.path.join(ROOT, "include", "raftcorr.h")
+    subprocess.check_call([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", header])
+    src = tmp_path / "use.c"
+    src.write_text('#include "raftcorr.h"\n#include <stdio.h>\n'
+                   'int main(void) {\n'
+                   '  raftcorr_level lv[RAFTCORR_MAX_LEVELS]; int64_t n[RAFTCORR_MAX_LEVELS];\n'
+                   '  if (raftcorr_pyramid_layout(1, 46, 62, 4, lv, n) != 0) return 1;\n'
+                   '  if (raftcorr_lookup_fwd(lv, 4, 0, 0, 1, 46, 62, 4, 0, 0) != RAFTCORR_E_INVALID) return 2;\n'
+                   '  printf("%d %d %d %s\\n", raftcorr_version(), lv[3].H, lv[3].W, raftcorr_last_error());\n'
+                   '  return 0;\n}\n')
+    exe = tmp_path / "use"
+    libdir = os.path.dirname(_capi.LIB_PATH)
+    subprocess.check_call([gcc, "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                           "-L", libdir, "-l:" + os.path.basename(_capi.LIB_PATH), "-Wl,-rpath," + libdir])
+    out = subprocess.check_output([str(exe)], text=True)
+    assert out.split()[1:3] == ["5", "7"] and "NULL" in out
