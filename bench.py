@@ -141,26 +141,39 @@ def synthetic_frames(batch, seed, pin=False):
 
 # ------------------------------------------------------------------------------------------------
 def run_cpu_reference(steps: int, warmup: int, sample_pairs: int = 1):
-    """The reference's CPU implementation of the path inside the harness model, on host cores."""
-    from oracle import torch_restatement as tr
+    """The reference's own CPU implementation of the path on the host cores: the UNMODIFIED core/raft.py +
+    core/corr.py from baseline/_ref (tools/install_ref.py; kind "reference").  Only when that copy is absent
+    does the oracle's torch restatement inside the harness model stand in (kind "port")."""
+    from harness import ref_model
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
-    model = make_model("cpu")
     im1, im2 = synthetic_frames(sample_pairs, seed=99)
-    factory = lambda f1, f2, r: tr.TorchCorrBlock(f1, f2, LEVELS, r)  # noqa: E731
+    if ref_model.available():
+        raft = ref_model.load_raft_module(dropin=False)
+        torch.manual_seed(1234)
+        ref = raft.RAFT(ref_model.make_args()).eval()
+        step = lambda: ref(im1, im2, iters=ITERS, test_mode=True)  # noqa: E731
+        kind, what = "reference", "the unmodified reference core/raft.py + core/corr.py (baseline/_ref) on CPU"
+    else:
+        from oracle import torch_restatement as tr
+        model = make_model("cpu")
+        factory = lambda f1, f2, r: tr.TorchCorrBlock(f1, f2, LEVELS, r)  # noqa: E731
+        step = lambda: model(im1, im2, factory, iters=ITERS)  # noqa: E731
+        kind, what = "port", ("oracle/torch_restatement.py (same ATen ops as core/corr.py) inside "
+                              "harness/raft_stock.py; baseline/_ref not installed")
     times = []
     with torch.no_grad():
         for i in range(warmup + steps):
             t0 = time.perf_counter()
-            model(im1, im2, factory, iters=ITERS)
+            step()
             dt = time.perf_counter() - t0
             if i >= warmup:
                 times.append(dt)
     total = sum(times)
     return {"value": sample_pairs * len(times) / total, "ms_per_step": 1e3 * total / len(times),
-            "cores": threads, "kind": "port",
+            "cores": threads, "kind": kind,
             "sample": f"{sample_pairs} frame pair(s) per step at 440x1024, 12 iterations, fp32, {len(times)} timed step(s); "
-                      "oracle/torch_restatement.py (same ATen ops as core/corr.py) inside harness/raft_stock.py"}
+                      + what}
 
 
 def measure_other_configs(dev, hbm_peak_gbs, model=None, frames=None):

@@ -1,6 +1,6 @@
-"""Pins the stock-PyTorch RAFT harness to the unmodified reference model (CPU; skipped where
-/root/reference is absent, e.g. on the GPU box), and the oracle's CorrBlock restatement inside
-the full 12-iteration loop."""
+"""Pins the stock-PyTorch RAFT harness to the unmodified reference model (CPU), and the oracle's CorrBlock
+restatement inside the full 12-iteration loop.  The reference tree is taken from baseline/_ref (the copy
+tools/install_ref.py makes, which travels to the GPU box) or from /root/reference; skipped when neither exists."""
 import argparse
 import os
 import sys
@@ -9,8 +9,10 @@ import warnings
 import pytest
 import torch
 
+from harness import ref_model
+
 warnings.filterwarnings("ignore")
-REF = "/root/reference/core"
+REF = ref_model.ref_core_dir() or "/root/reference/core"
 
 
 @pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree not present")
