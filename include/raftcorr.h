@@ -14,7 +14,10 @@
  *    device; kernels are enqueued on `stream` (a cudaStream_t passed as void*; NULL = the
  *    legacy default stream).  All pointers are device pointers on the current device unless
  *    the name says host.
- *  - re-entrant: no mutable global state (nn.DataParallel calls it from one thread per GPU).
+ *  - re-entrant (nn.DataParallel calls it from one thread per GPU): no per-call state is kept.  What the
+ *    library does keep is caches behind mutexes - encoded TMA tensor maps (a small LRU keyed on pointers,
+ *    sizes and strides), per-device SM counts / kernel attributes - and, for the one entry point that says so
+ *    (raftcorr_build_pyramid_noalloc), a fixed scratch array shared by all its calls on a device.
  */
 #ifndef RAFTCORR_H_
 #define RAFTCORR_H_
@@ -73,7 +76,8 @@ int raftcorr_build_pyramid(const float* fmap1, const float* fmap2, int B, int D,
                            int num_levels, const raftcorr_level* levels, int precision,
                            void* workspace, int64_t workspace_bytes, void* stream);
 
-/* Same result as raftcorr_build_pyramid at RAFTCORR_PREC_BF16 / RAFTCORR_PREC_TF32, for callers that
+/* Same result as raftcorr_build_pyramid at RAFTCORR_PREC_BF16 / RAFTCORR_PREC_TF32 (including its fp32
+ * CUDA-core build, which needs no scratch, when D % 8 != 0), for callers that
  * cannot hand over a workspace.  This entry point has no counterpart in the reference.
  * Who needs it: a host that claims the whole device for its own pool at start-up and passes a
  * plug-in only input/output pointers (the binding has no way to ask that pool for more), or a

@@ -57,8 +57,10 @@ class CorrBlock:
         return ops.lookup(self._holder["pyr"], coords, self.radius, self._coord_mode, self._channels_last)
 
     def lookup_conv1x1(self, coords, weight, bias=None, relu=True):
-        """Extra: ``relu(conv1x1(self(coords)))`` — the lookup fused with the first layer of the
-        motion encoder (``convc1``, core/update.py:83,90) — without ever forming the (B, 324, H, W) tensor.
+        """Extra: ``relu(conv1x1(self(coords)))`` — the lookup followed by the first layer of the
+        motion encoder (``convc1``, core/update.py:83,90) behind one call.  Two launches: the samples are written
+        once, query-major ((B, H, W, 324) in a scratch buffer), and a tcgen05 GEMM with bias + ReLU in its epilogue
+        reads them back; the NCHW (B, 324, H, W) tensor and the separate bias / ReLU passes are what is saved.
         ``weight`` is the convolution's (out_channels, 324, 1, 1) weight.  TF32 products; inference only."""
         if torch.is_grad_enabled() and (coords.requires_grad or weight.requires_grad or
                                         (self._token is not None and self._token.requires_grad)):

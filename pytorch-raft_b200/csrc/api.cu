@@ -155,6 +155,9 @@ int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B
              "build_pyramid_noalloc: precision must be RAFTCORR_PREC_BF16 or RAFTCORR_PREC_TF32 "
              "(the fp32 build needs no workspace: call raftcorr_build_pyramid)");
   if (int rc = check_levels(levels, num_levels, H, W, "build_pyramid_noalloc")) return rc;
+  // channel counts the tensor-core operand layout cannot take go to the fp32 CUDA-core build, exactly as in
+  // raftcorr_build_pyramid; that build uses no scratch memory at all
+  if (D % 8 != 0) return launch_build_fp32(fmap1, fmap2, B, D, H, W, num_levels, levels, (cudaStream_t)stream);
   return launch_build_tc_noalloc(fmap1, fmap2, B, D, H, W, num_levels, levels, precision,
                                  (cudaStream_t)stream);
 }

@@ -3,8 +3,10 @@
 // The reference gets this from autograd: AvgPool2DBackward0 x3 spreads each
 // pooled gradient over its 2x2 parents (/4), DivBackward0 applies 1/sqrt(D), BmmBackward0 forms
 //   d f1[b,d,i] = sum_j dC[b,i,j] f2[b,d,j]      d f2[b,d,j] = sum_i dC[b,i,j] f1[b,d,i].
-// Here the un-pool + scale is one pass that materialises dC in the caller's workspace, followed
-// by two fp32 FMA GEMMs (gradients are checked at rtol 1e-3, so they stay fp32).
+// Here the un-pool + scale is one pass that materialises dC in the caller's workspace as tf32 hi/lo
+// splits (plain and transposed), followed by two split-tf32 tcgen05 GEMMs (hi*hi + hi*lo + lo*hi:
+// fp32-accurate, gradients are checked at rtol 1e-3); shapes TMA cannot address (H*W % 4 != 0) take
+// the fp32 CUDA-core GEMMs further down.
 #include "common.cuh"
 
 namespace raftcorr {

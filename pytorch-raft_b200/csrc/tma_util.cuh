@@ -31,9 +31,21 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// Bounded wait: a protocol bug must surface as a launch failure, never as a hung GPU.
+// Bounded wait: a protocol bug must surface as a launch failure, never as a hung GPU.  The bound is
+// wall-clock time (%globaltimer, nanoseconds) and generous - RAFTCORR_WAIT_LIMIT_NS, one minute by
+// default - so that a context that is merely time-sliced out on a shared GPU, or stopped under a
+// debugger / compute-sanitizer, is not mistaken for a deadlock (an SM cycle counter keeps running
+// through all of those and a 4-second budget of it is easy to exhaust legitimately).
 // With -DRAFTCORR_DEBUG_TIMEOUT the wait gives up quickly, records who waited on what in
 // g_wait_timeout and lets the kernel run on (garbage results, but it terminates and can be read).
+#ifndef RAFTCORR_WAIT_LIMIT_NS
+#define RAFTCORR_WAIT_LIMIT_NS 60000000000ULL
+#endif
+__device__ __forceinline__ unsigned long long wall_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
 #ifdef RAFTCORR_DEBUG_TIMEOUT
 __device__ unsigned long long g_wait_timeout[8];
 #endif
@@ -50,7 +62,11 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int tag = 0) {
   if (mbar_try(bar, parity)) return;
+#ifdef RAFTCORR_DEBUG_TIMEOUT
   const long long t0 = clock64();
+#else
+  unsigned long long t0 = 0;   // read lazily: the common wait ends long before the clock is needed
+#endif
   for (uint32_t spins = 1;; ++spins) {
     if (mbar_try(bar, parity)) return;
     if ((spins & 63u) == 0) {   // the clock is only consulted now and then: keep the spin cheap
@@ -65,7 +81,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int tag
       }
 #else
       (void)tag;
-      if (clock64() - t0 > 8000000000LL) __trap();
+      const unsigned long long now = wall_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > RAFTCORR_WAIT_LIMIT_NS) __trap();
 #endif
     }
   }
@@ -74,7 +92,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, int tag
 // the spin does not steal issue slots from the warps doing the work
 __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity, int tag = 0) {
   if (mbar_try(bar, parity)) return;
+#ifdef RAFTCORR_DEBUG_TIMEOUT
   const long long t0 = clock64();
+#else
+  unsigned long long t0 = 0;
+#endif
   for (uint32_t spins = 1;; ++spins) {
     __nanosleep(256);
     if (mbar_try(bar, parity)) return;
@@ -83,7 +105,9 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, uint32_t parity,
       if (clock64() - t0 > 100000000LL) return;
 #else
       (void)tag;
-      if (clock64() - t0 > 8000000000LL) __trap();
+      const unsigned long long now = wall_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > RAFTCORR_WAIT_LIMIT_NS) __trap();
 #endif
     }
   }

@@ -218,15 +218,31 @@ def alt_backward(fmap1, fmap2, coords, corr_grad, radius: int, coord_mode=COORD_
 # ---- autograd -------------------------------------------------------------------------------
 class _GradSink:
     """Shared d(pyramid) accumulator: every lookup of one CorrBlock scatters into the same
-    buffers instead of materialising a volume-sized gradient per iteration."""
+    buffers instead of materialising a volume-sized gradient per iteration.
+
+    The accumulated gradient belongs to ONE backward pass: BuildFn.backward consumes and drops it.  A pass that
+    scatters but never reaches BuildFn (``torch.autograd.grad(out, coords)`` prunes that node; an exception can
+    abort the pass) must not leave its partial sums behind for the next pass to inherit, so the first scatter of
+    a pass queues an end-of-pass callback with the autograd engine that drops whatever is still here."""
 
     def __init__(self):
         self.grad_pyr: Optional[Pyramid] = None
+        self._pass_open = False
 
     def buffers(self, like: Pyramid, device) -> Pyramid:
         if self.grad_pyr is None:
             self.grad_pyr = Pyramid(like.B, like.H, like.W, like.num_levels, device, zero=True)
+        if not self._pass_open:
+            self._pass_open = True
+            try:   # only valid while the engine is running a backward pass - which is when this is called
+                torch.autograd.Variable._execution_engine.queue_callback(self.end_of_pass)
+            except RuntimeError:
+                self._pass_open = False
         return self.grad_pyr
+
+    def end_of_pass(self):
+        self.grad_pyr = None
+        self._pass_open = False
 
 
 class BuildFn(torch.autograd.Function):
@@ -253,7 +269,7 @@ class BuildFn(torch.autograd.Function):
             if g is not None:
                 gp.storage[l][:, :, : gp.desc[l].W].add_(g.squeeze(1))
         g1, g2 = build_backward(gp, fmap1, fmap2)
-        sink.grad_pyr = None
+        sink.grad_pyr = None     # consumed (the end-of-pass callback then finds nothing to drop)
         return g1, g2, None, None, None
 
 

@@ -72,6 +72,28 @@ def test_twelve_lookups_share_one_gradient_buffer(golden):
         assert np.allclose(got.cpu().numpy(), ref, rtol=1e-3, atol=1e-4 * np.abs(ref).max())
 
 
+def test_partial_backward_leaves_nothing_behind():
+    """A backward pass that scatters into the shared d(pyramid) buffers but never reaches the build node
+    (torch.autograd.grad w.r.t. coords prunes it) must not leak its sums into the next, full pass."""
+    import corr
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    f1 = torch.randn(1, 32, 16, 24, device="cuda", generator=gen, requires_grad=True)
+    f2 = torch.randn(1, 32, 16, 24, device="cuda", generator=gen, requires_grad=True)
+    ys, xs = torch.meshgrid(torch.arange(16.0), torch.arange(24.0), indexing="ij")
+    c = (torch.stack([xs, ys])[None] + 0.3).cuda().requires_grad_(True)
+    up = torch.randn(1, 324, 16, 24, device="cuda", generator=gen)
+
+    blk = corr.CorrBlock(f1, f2)
+    out = blk(c)
+    (gc,) = torch.autograd.grad(out, c, up, retain_graph=True)      # scatters, BuildFn.backward never runs
+    assert torch.isfinite(gc).all()
+    out.backward(up)                                                 # the full pass
+    got1, got2 = f1.grad.clone(), f2.grad.clone()
+    f1.grad = f2.grad = c.grad = None
+    corr.CorrBlock(f1, f2)(c).backward(up)                           # a fresh block, one pass
+    assert torch.equal(got1, f1.grad) and torch.equal(got2, f2.grad)
+
+
 def test_no_grad_builds_no_graph(golden):
     import corr
     g = golden("corr_tiny")

@@ -28,11 +28,14 @@ def _build_both(fmap1, fmap2, precision):
     out = ops.Pyramid(B, H, W, 4, fmap1.device, zero=True)       # caller-owned outputs
     torch.cuda.synchronize()
     before = torch.cuda.memory_allocated()
+    free_before, _ = torch.cuda.mem_get_info()    # cudaMemGetInfo: sees raw cudaMalloc too, not only torch's pool
     rc = lib.raftcorr_build_pyramid_noalloc(fmap1.data_ptr(), fmap2.data_ptr(), B, D, H, W, 4, out.desc, prec,
                                             ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     assert rc == 0, lib.raftcorr_last_error()
     torch.cuda.synchronize()
     assert torch.cuda.memory_allocated() == before   # nothing went through torch's allocator either
+    free_after, _ = torch.cuda.mem_get_info()
+    assert free_after >= free_before, (free_before, free_after)   # ... and nothing was taken from the device
     return ref, out
 
 
@@ -50,6 +53,13 @@ def test_noalloc_matches_workspace_build_twice_in_a_row(precision):
             err = (a - b).abs().max().item() / b.abs().max().item()
             assert err <= TOL, (precision, shape, l, err)
             assert torch.equal(a, b)   # same kernels, same operands: in fact bit-identical
+        if shape == shapes[-1]:    # ... and once against the checker itself, not only against the sibling entry point
+            import oracle
+            want = oracle.build_pyramid(f1.cpu(), f2.cpu(), 4)
+            for l in range(4):
+                got = out.views()[l].cpu().numpy()
+                assert got.shape == want[l].shape
+                assert abs(got - want[l]).max() <= TOL * abs(want[l]).max(), (precision, l)
 
 
 def test_noalloc_rejects_what_does_not_fit():
@@ -68,3 +78,17 @@ def test_noalloc_rejects_what_does_not_fit():
     assert "scratch" in msg and str(_capi.NOALLOC_SCRATCH_BYTES) in msg
     rc = lib.raftcorr_build_pyramid_noalloc(f.data_ptr(), f.data_ptr(), 1, 8, 16, 16, 4, lv, _capi.PREC_FP32, None)
     assert rc == -1 and b"precision" in lib.raftcorr_last_error()
+
+
+def test_noalloc_odd_channel_count_takes_the_scratch_free_build():
+    """D % 8 != 0 cannot use the tensor-core operand layout; like raftcorr_build_pyramid the entry point then
+    runs the fp32 CUDA-core build (which needs no scratch) instead of refusing."""
+    import oracle
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    f1 = torch.randn(1, 12, 16, 24, device="cuda", generator=gen)
+    f2 = torch.randn(1, 12, 16, 24, device="cuda", generator=gen)
+    _, out = _build_both(f1, f2, "bf16")
+    want = oracle.build_pyramid(f1.cpu(), f2.cpu(), 4)
+    for l in range(4):
+        got = out.views()[l].cpu().numpy()
+        assert abs(got - want[l]).max() <= 1e-5 * abs(want[l]).max(), l
