@@ -96,6 +96,34 @@ int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B
                                    int num_levels, const raftcorr_level* levels, int precision,
                                    void* stream);
 
+/* ---- (1b) the same pyramid in 16-bit storage: core/corr.py:21-27 stores fp32, which makes
+ *      the build HBM-write bound (5.3 B written per 512 flop) and the lookup read 4-byte pixels out of 64-byte
+ *      DRAM granules.  Here every level holds bfloat16 pixels in blocks of 4 rows x 8 columns = 64 bytes (one
+ *      DRAM granule; a 10x10 window touches ~7 of them instead of ~13 row pieces):
+ *        pixel (y, x) of image n lives at byte  n*image_stride + ((y>>2)*blocks_x + (x>>3))*64 + (y&3)*16 + (x&7)*2
+ *      with blocks_x = ceil(W/8), blocks_y = ceil(H/4), image_stride = blocks_x*blocks_y*64.  Pixels of a block
+ *      that lie outside the H x W image are stored as +0.0 (the lookup relies on it: they are grid_sample's zero
+ *      padding).  Values: bf16 tcgen05 products, fp32 accumulation and pooling, one rounding to bf16 per stored
+ *      pixel: <= 1e-2 of max|ref| like RAFTCORR_PREC_BF16.  Inference only (gradients use the fp32 pyramid). */
+typedef struct raftcorr_level16 {
+  void* data;           /* bfloat16, 64-byte aligned                    */
+  int32_t H, W;         /* pixels                                       */
+  int32_t blocks_x, blocks_y;
+  int64_t image_stride; /* bytes between images = blocks_x*blocks_y*64  */
+} raftcorr_level16;
+/* Fills H/W/blocks_x/blocks_y/image_stride of levels[0..L) (data untouched); bytes_per_level[l] = B*H*W images. */
+int raftcorr_pyramid16_layout(int B, int H, int W, int num_levels, raftcorr_level16* levels,
+                              int64_t* bytes_per_level);
+/* Build (replaces core/corr.py:13-27, 52-60).  Needs D % 8 == 0 (else RAFTCORR_E_UNSUPPORTED: use the fp32
+ * pyramid).  workspace: raftcorr_build_workspace_bytes(B, D, H, W, RAFTCORR_PREC_BF16) bytes, 256-byte aligned. */
+int raftcorr_build_pyramid16(const float* fmap1, const float* fmap2, int B, int D, int H, int W,
+                             int num_levels, const raftcorr_level16* levels, void* workspace,
+                             int64_t workspace_bytes, void* stream);
+/* Lookup on it (replaces core/corr.py:29-50; same semantics, layouts and channel order as raftcorr_lookup_fwd;
+ * bit-identical to the reference's arithmetic applied to the stored bf16 values).  num_levels == 4, radius 3 or 4. */
+int raftcorr_lookup16_fwd(const raftcorr_level16* levels, int num_levels, const float* coords, float* out,
+                          int B, int H, int W, int radius, int coord_mode, void* stream);
+
 /* ---- (2) 4-level (2r+1)^2 bilinear window lookup: replaces CorrBlock.__call__
  *      (core/corr.py:29-50) including bilinear_sampler (core/utils/utils.py:57-65) and
  *      grid_sample(align_corners=True, zero padding).

@@ -54,6 +54,10 @@ struct BuildTcParams {
   const float* bias;
   int relu;
   int a_batch_mul;    // 1: A has a batch dimension; 0: one A for every batch
+  // 16-bit blocked pyramid (raftcorr_level16): block grid per level, and level 3 for plain stores
+  int bxs[RAFTCORR_MAX_LEVELS], bys[RAFTCORR_MAX_LEVELS];
+  unsigned char* l3_data;
+  long long l3_istride;   // bytes
 };
 
 // Stage one row segment (kNF floats per query, 32 queries) in swizzled shared memory and hand it
@@ -92,7 +96,29 @@ struct alignas(64) TcOperandMaps {
   CUtensorMap b[3];
 };
 
-template <bool kTf32>
+// ---- epilogue of the 16-bit blocked pyramid (include/raftcorr.h, raftcorr_level16) ---------------------------
+// A staged box is 32 queries x kRowBytes; lane = query.  Chunks of 16 bytes are placed with the TMA swizzle of
+// the box's tensor map (128-byte rows: SWIZZLE_128B, 32-byte rows: SWIZZLE_32B) so a quarter warp fills whole
+// 128-byte wavefronts.
+__device__ __forceinline__ uint32_t stage16_begin(uint32_t buf_base, uint32_t& nstores, int lane) {
+  const uint32_t buf = buf_base + (nstores & 1) * kEpiBufBytes;
+  ++nstores;
+  if (lane == 0) bulk_wait_read<1>();  // the store issued two boxes ago has drained this buffer
+  __syncwarp();
+  return buf;
+}
+template <int kRowBytes>
+__device__ __forceinline__ void stage16_chunk(uint32_t buf, int lane, int c, uint32_t a, uint32_t b, uint32_t cc,
+                                              uint32_t d) {
+  int phys = c;
+  if (kRowBytes == 128) phys = c ^ (lane & 7);
+  if (kRowBytes == 32) phys = c ^ ((lane >> 2) & 1);
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf + lane * kRowBytes + phys * 16), "r"(a), "r"(b),
+               "r"(cc), "r"(d)
+               : "memory");
+}
+
+template <bool kTf32, bool kOut16>
 __global__ void __launch_bounds__(kThreads, 1)
 build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
                 const __grid_constant__ CUtensorMap mapL0, const __grid_constant__ CUtensorMap mapL1,
