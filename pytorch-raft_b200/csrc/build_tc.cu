@@ -252,6 +252,142 @@ build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
         }
         continue;
       }
+      if constexpr (kOut16) {
+        // bf16 pixels in 4x8 blocks.  An 8x32 tile is 2 block rows x 4 blocks at level 0, one block row x 2
+        // blocks at level 1, half a block at level 2 and a quarter of a block row at level 3.
+        uint32_t prev[32], l1pk[32];
+        float q1[2][16], q2[2][8];
+        const bool edge = (x0 + kTileX > p.W) | (y0 + kTileY > p.H);   // pooled patches reach padding pixels
+#pragma unroll
+        for (int rp = 0; rp < 4; ++rp) {
+          float f[64];
+          tmem_ld_x64(taddr + rp * 64, f);
+          tmem_ld_wait();
+          if (rp == 3) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar(group));
+          }
+          if (!rows_live) continue;
+#pragma unroll
+          for (int c = 0; c < 64; ++c) f[c] *= p.inv_scale;  // corr.py:60 (pixels beyond H x W are exact zeros:
+                                                             // TMA zero-filled their fmap2 rows)
+          uint32_t cur[32];
+#pragma unroll
+          for (int k = 0; k < 32; ++k) cur[k] = pack_bf16x2(f[2 * k], f[2 * k + 1]);
+          // 2x2 means in fp32, ATen's order ((a+b)+c)+d then /4 (corr.py:26); padding pixels of the pooled levels
+          // (x >= W_l or y >= H_l, reachable only from edge tiles) must be stored as zeros
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            q1[rp & 1][k] = (((f[2 * k] + f[2 * k + 1]) + f[32 + 2 * k]) + f[33 + 2 * k]) * 0.25f;
+          if (edge) {
+            const bool row_ok = (y0 >> 1) + rp < p.Hl[1];
+#pragma unroll
+            for (int k = 0; k < 16; ++k)
+              if (!row_ok || (x0 >> 1) + k >= p.Wl[1]) q1[rp & 1][k] = 0.0f;
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) l1pk[rp * 8 + k] = pack_bf16x2(q1[rp & 1][2 * k], q1[rp & 1][2 * k + 1]);
+          if (rp & 1) {
+            const int by = (y0 >> 2) + (rp >> 1);
+            if (by < p.bys[0]) {
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                const int bx = (x0 >> 3) + 2 * h;
+                if (bx >= p.bxs[0]) continue;
+                const uint32_t buf = stage16_begin(buf_base, nstores, lane);
+#pragma unroll
+                for (int bl = 0; bl < 2; ++bl)
+#pragma unroll
+                  for (int r = 0; r < 4; ++r) {
+                    const uint32_t* src = (r < 2 ? prev : cur) + (r & 1) * 16 + (2 * h + bl) * 4;
+                    stage16_chunk<128>(buf, lane, bl * 4 + r, src[0], src[1], src[2], src[3]);
+                  }
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                  tma_store_4d(&mapL0, buf, bx * 32, by, q0, b);
+                  bulk_commit();
+                }
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              q2[rp >> 1][k] = (((q1[0][2 * k] + q1[0][2 * k + 1]) + q1[1][2 * k]) + q1[1][2 * k + 1]) * 0.25f;
+            if (edge) {
+              const bool row_ok = (y0 >> 2) + (rp >> 1) < p.Hl[2];
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                if (!row_ok || (x0 >> 2) + k >= p.Wl[2]) q2[rp >> 1][k] = 0.0f;
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 32; ++k) prev[k] = cur[k];
+          }
+        }
+        if (!rows_live) continue;
+        if (p.L > 1 && ty < p.bys[1] && 2 * tx < p.bxs[1]) {     // level 1: block row ty, blocks 2tx, 2tx+1
+          const uint32_t buf = stage16_begin(buf_base, nstores, lane);
+#pragma unroll
+          for (int bl = 0; bl < 2; ++bl)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              const uint32_t* src = l1pk + r * 8 + bl * 4;
+              stage16_chunk<128>(buf, lane, bl * 4 + r, src[0], src[1], src[2], src[3]);
+            }
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_4d(&mapL1, buf, 2 * tx * 32, ty, q0, b);
+            bulk_commit();
+          }
+        }
+        if (p.L > 2 && (ty >> 1) < p.bys[2] && tx < p.bxs[2]) {  // level 2: rows 2(ty&1), +1 of block (ty>>1, tx)
+          // the level is addressed in 32-byte half blocks: unit = 2 * block + half
+          const int unit = 2 * ((ty >> 1) * p.bxs[2] + tx) + (ty & 1);
+          const bool tail = (ty == p.tiles_y - 1) && !(ty & 1);  // nobody else writes the block's lower half
+#pragma unroll
+          for (int part = 0; part < 2; ++part) {
+            if (part == 1 && !tail) break;
+            const uint32_t buf = stage16_begin(buf_base, nstores, lane);
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+              uint32_t w[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) w[k] = part ? 0u : pack_bf16x2(q2[r][2 * k], q2[r][2 * k + 1]);
+              stage16_chunk<32>(buf, lane, r, w[0], w[1], w[2], w[3]);
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_4d(&mapL2, buf, 0, unit + part, q0, b);
+              bulk_commit();
+            }
+          }
+        }
+        if (p.L > 3 && (ty >> 2) < p.bys[3] && (tx >> 1) < p.bxs[3] && q0 + lane < p.N) {
+          // level 3: row ty, columns 4tx..4tx+3 = 8 bytes per query, plain stores.  The last tile row / column
+          // also zero what is left of the block (rows below, the block's other four columns).
+          float q3[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            q3[k] = (((q2[0][2 * k] + q2[0][2 * k + 1]) + q2[1][2 * k]) + q2[1][2 * k + 1]) * 0.25f;
+            if (ty >= p.Hl[3] || 4 * tx + k >= p.Wl[3]) q3[k] = 0.0f;
+          }
+          unsigned char* blk = p.l3_data + ((long long)b * p.N + q0 + lane) * p.l3_istride +
+                               ((long long)(ty >> 2) * p.bxs[3] + (tx >> 1)) * 64;
+          const uint2 v = make_uint2(pack_bf16x2(q3[0], q3[1]), pack_bf16x2(q3[2], q3[3]));
+          const int colb = (tx & 1) * 8;
+          const bool zero_cols = (tx == p.tiles_x - 1) && !(tx & 1);
+          const int row_end = (ty == p.tiles_y - 1) ? 4 : (ty & 3) + 1;
+          for (int r = ty & 3; r < row_end; ++r) {
+            const uint2 w = r == (ty & 3) ? v : make_uint2(0u, 0u);
+            *reinterpret_cast<uint2*>(blk + r * 16 + colb) = w;
+            if (zero_cols) *reinterpret_cast<uint2*>(blk + r * 16 + 8) = make_uint2(0u, 0u);
+          }
+        }
+        continue;
+      }
       float p1[2][16];
       float p2[2][8];
 #pragma unroll
@@ -426,19 +562,22 @@ int64_t build_tc_workspace_bytes(int B, int D, int H, int W, int precision) {
 
 // Shared launcher of build_tc_kernel: operand maps for `passes` (A, B) pairs are already encoded.
 static int launch_tc_kernel(bool tf32, const TcOperandMaps& ops, const CUtensorMap* out_maps, const BuildTcParams& p,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, bool out16 = false) {
   int dev = 0, sms = 0;
   RC_CHECK_CUDA(cudaGetDevice(&dev));
   RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const long long total = (long long)p.B * p.tiles_m * p.tiles_y * p.tiles_x;
   if (total == 0) return 0;
   const int grid = (int)(total < sms ? total : sms);
-  if (!tf32) {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
+  if (out16) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<false, true><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
+  } else if (!tf32) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<false, false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
   } else {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<true><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<true, false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
   }
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -541,6 +680,9 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   p.bias = nullptr;
   p.relu = 0;
   p.a_batch_mul = 1;
+  p.l3_data = nullptr;
+  p.l3_istride = 0;
+  for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) p.bxs[l] = p.bys[l] = 0;
   p.idesc = make_idesc(tf32);
   p.inv_scale = 1.0f / sqrtf((float)D);
   for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
@@ -613,6 +755,9 @@ int launch_tc_gemm_any(const float* const* a_src, const float* const* b_src, int
   p.bias = bias;
   p.relu = relu;
   p.a_batch_mul = a_shared ? 0 : 1;
+  p.l3_data = nullptr;
+  p.l3_istride = 0;
+  for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) p.bxs[l] = p.bys[l] = 0;
   for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
     p.Hl[l] = 1;
     p.Wl[l] = Nn;
