@@ -692,6 +692,92 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   return launch_tc_kernel(tf32, ops, mapL, p, stream);
 }
 
+// The same build into the 16-bit blocked pyramid (raftcorr_level16): bf16 operands, fp32 accumulation and
+// pooling in TMEM / registers, one rounding to bf16 per stored pixel.  Halves the bytes the epilogue writes.
+int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int W, int L,
+                      const raftcorr_level16* levels, void* ws, int64_t ws_bytes, cudaStream_t stream) {
+  const int N = H * W;
+  if (B == 0) return 0;
+  if (D % 8 != 0)
+    return fail(RAFTCORR_E_UNSUPPORTED, "build_pyramid16: needs D %% 8 == 0 (D=%d); use the fp32 pyramid", D);
+  const int64_t need = build_tc_workspace_bytes(B, D, H, W, RAFTCORR_PREC_BF16);
+  if (ws == nullptr || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 255))
+    return fail(RAFTCORR_E_WORKSPACE, "build_pyramid16: workspace must be 256-byte aligned and >= %lld B", (long long)need);
+  char* wsb = static_cast<char*>(ws);
+  const int64_t one = align256((int64_t)B * N * D * 2);
+  void* packA = wsb;
+  void* packB = wsb + one;
+  dim3 g2((N + 63) / 64, (D + 63) / 64, 2 * B);
+  pack2_bf16_kernel<<<g2, 256, 0, stream>>>(f1, f2, static_cast<__nv_bfloat16*>(packA), static_cast<__nv_bfloat16*>(packB), D, N);
+  RC_CHECK_CUDA(cudaGetLastError());
+
+  TcOperandMaps ops;
+  for (int ps = 0; ps < 3; ++ps) {
+    {
+      cuuint64_t dims[3] = {(cuuint64_t)D, (cuuint64_t)N, (cuuint64_t)B};
+      cuuint64_t strides[2] = {(cuuint64_t)D * 2, (cuuint64_t)N * D * 2};
+      cuuint32_t box[3] = {64, kBlockM, 1};
+      if (int rc = encode(&ops.a[ps], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, packA, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "A")) return rc;
+    }
+    {
+      cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+      cuuint64_t strides[3] = {(cuuint64_t)D * 2, (cuuint64_t)W * D * 2, (cuuint64_t)N * D * 2};
+      cuuint32_t box[4] = {64, kTileX, kTileY, 1};
+      if (int rc = encode(&ops.b[ps], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, packB, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "B")) return rc;
+    }
+  }
+  CUtensorMap mapL[RAFTCORR_MAX_LEVELS];
+  for (int l = 0; l < 2; ++l) {   // levels 0, 1: two whole blocks (128 B) per query per box
+    // A block row of an image is contiguous (blocks_x * 64 B), so the two innermost axes (pixel in block, block
+    // column) are one axis of blocks_x * 32 elements: the box's inner row is then exactly the 128-byte swizzle span
+    // (a 64-byte inner axis would be padded to 128-byte rows in shared memory: tools/probe/tma_swizzle_probe.cu),
+    // and TMA clips the second block of a pair at the end of the block row.
+    const raftcorr_level16& lv = levels[l < L ? l : 0];
+    cuuint64_t dims[4] = {(cuuint64_t)lv.blocks_x * 32, (cuuint64_t)lv.blocks_y, (cuuint64_t)N, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)lv.blocks_x * 64, (cuuint64_t)lv.image_stride, (cuuint64_t)lv.image_stride * N};
+    cuuint32_t box[4] = {64, 1, 32, 1};
+    if (int rc = encode(&mapL[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, lv.data, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "level16"))
+      return rc;
+  }
+  {                               // level 2: 32-byte half blocks (rows 0-1 / 2-3 of a block), one per query per box
+    const raftcorr_level16& lv = levels[2 < L ? 2 : 0];
+    cuuint64_t dims[4] = {16, (cuuint64_t)lv.blocks_x * lv.blocks_y * 2, (cuuint64_t)N, (cuuint64_t)B};
+    cuuint64_t strides[3] = {32, (cuuint64_t)lv.image_stride, (cuuint64_t)lv.image_stride * N};
+    cuuint32_t box[4] = {16, 1, 32, 1};
+    if (int rc = encode(&mapL[2], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, lv.data, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_32B, "level16 half blocks"))
+      return rc;
+    mapL[3] = mapL[2];            // level 3 is written with plain stores
+  }
+
+  BuildTcParams p;
+  p.B = B;
+  p.N = N;
+  p.H = H;
+  p.W = W;
+  p.L = L;
+  p.tiles_m = (N + kBlockM - 1) / kBlockM;
+  p.tiles_y = (H + kTileY - 1) / kTileY;
+  p.tiles_x = (W + kTileX - 1) / kTileX;
+  p.k_elems = 64;
+  p.k_blocks = (D + 63) / 64;
+  p.passes = 1;
+  p.plain = 0;
+  p.bias = nullptr;
+  p.relu = 0;
+  p.a_batch_mul = 1;
+  p.idesc = make_idesc(false);
+  p.inv_scale = 1.0f / sqrtf((float)D);
+  for (int l = 0; l < RAFTCORR_MAX_LEVELS; ++l) {
+    p.Hl[l] = H >> l;
+    p.Wl[l] = W >> l;
+    p.bxs[l] = l < L ? levels[l].blocks_x : 0;
+    p.bys[l] = l < L ? levels[l].blocks_y : 0;
+  }
+  p.l3_data = L > 3 ? static_cast<unsigned char*>(levels[3].data) : nullptr;
+  p.l3_istride = L > 3 ? levels[3].image_stride : 0;
+  return launch_tc_kernel(false, ops, mapL, p, stream, true);
+}
+
 // Batched fp32-accurate GEMM on the tf32 tensor pipe (plain epilogue), used by build_bwd.cu:
 //   C[b][m][n] = sum_k A[b][m][k] * B[b][n][k]      A = a_hi + a_lo, B = b_hi + b_lo (tf32 values)
 // All operands are K-major fp32 with row pitches / batch strides in elements; pitches and o_pitch
