@@ -1,0 +1,323 @@
+// lookup16.cu — the pyramid window lookup on the 16-bit blocked pyramid (raftcorr_level16), sm_100a.
+//
+// Same arithmetic as lookup.cu / lookup_tma.cu (reference core/corr.py:29-50 + core/utils/utils.py:57-65 +
+// ATen grid_sampler_2d, replayed op for op), different decomposition.  Measured on the fp32 kernel
+// (profiles/r01_*): one warp per query spends ~635 warp-instructions per query, most of them per-query
+// bookkeeping that only one or a few lanes really need (tap tables, window geometry, TMA issue, barrier
+// traffic, the shared-memory transpose of the output), and the kernel is bound by issue slots, not by DRAM.
+// Here a LANE owns a query:
+//
+//   unit      = 32 consecutive-x queries of one fmap row at ONE pyramid level (4 units per tile)
+//   producers = 4 warps, one per level: lane q derives its query's window, the warp issues one TMA box per
+//               lane (cp.async.bulk.tensor.4d over the level's (64-byte block, blocks_x, blocks_y, image)
+//               tensor: {2,3} x {3,4} whole blocks; out-of-image blocks arrive as zeros = grid_sample's zero
+//               padding) into the lane's slot of a unit buffer, all 32 boxes on one mbarrier
+//   samplers  = 8 warps, a pair per level (the pair splits the x taps): lane q forms its query's (2r+1)^2
+//               samples out of its own slot and stores them straight to the NCHW output — for a fixed channel
+//               the 32 lanes are 32 consecutive x, so every store instruction is one full 128-byte line and
+//               the output never passes through shared memory
+//
+// Shared memory: 7 unit buffers x 32 slots x 896 B.  The 32 windows are walked in lock step, at the same
+// in-window offset more often than not, and TMA wants 128-byte aligned destinations, so unskewed slots would put
+// all lanes on one bank.  The boxes are therefore fetched with the 64-byte TMA swizzle (16-byte chunk index
+// bits 4-5 ^= address bits 7-8; measured layout: tools/probe/tma_swizzle_probe.cu — the 128-byte swizzle pads
+// every 64-byte block to a 128-byte row and would double the footprint) at a slot pitch that is an odd multiple
+// of 128 B: four skew classes.  The slot order puts lanes whose windows start one pixel apart at their level
+// into the same class, so that class mates fall on different words.
+#include <string.h>
+
+#include <atomic>
+#include <mutex>
+
+#include "lookup_common.cuh"
+#include "tma_util.cuh"
+
+namespace raftcorr {
+
+namespace {
+
+using namespace lk;
+
+constexpr int kL = RAFTCORR_MAX_LEVELS;           // the kernel is specialised for the 4-level pyramid
+constexpr int kSamplers16 = 8;
+constexpr int kProducers16 = 4;
+constexpr int kThreads16 = (kSamplers16 + kProducers16) * 32;
+constexpr int kBufs = 7;
+constexpr int kSlot = 896;                         // 7 x 128 B >= the largest box (3 x 4 blocks = 768 B)
+constexpr int kBufBytes = 32 * kSlot;              // 28 KB: a multiple of 1024, so swizzle phases are slot-relative
+constexpr int kOffBars16 = kBufs * kBufBytes;
+constexpr int kSmem16 = kOffBars16 + 2 * kBufs * 8;
+
+struct Level16Dev {
+  const unsigned char* data;
+  int H, W, bxs, bys;
+  long long istride;                                // bytes
+  float sm1x, invx, halfx, sm1y, invy, halfy, inv_pow2;
+};
+
+struct Lookup16Params {
+  Level16Dev lv[kL];
+  const float* coords;
+  float* out;
+  int B, H, W, tiles_x;
+  long long tiles;
+};
+
+// box shapes: [level][wide: 2 or 3 blocks][tall: 3 or 4 block rows]
+struct alignas(64) Lookup16Maps {
+  CUtensorMap m[kL][2][2];
+};
+
+// slot of lane q in a unit buffer (a permutation of 0..31 per level; skew class = slot & 3): class mates are
+// 8 lanes whose queries are 1, 2, 4 (4) fmap pixels apart at level 0, 1, 2 (3), i.e. ~one level pixel
+__device__ __forceinline__ int slot_of(int lane, int level) {
+  if (level == 0) return ((lane & 7) << 2) | (lane >> 3);
+  if (level == 1) return (((lane >> 1) & 7) << 2) | (((lane >> 4) & 1) << 1) | (lane & 1);
+  return lane;
+}
+// physical shared-memory address of logical byte `a` of a box fetched with CU_TENSOR_MAP_SWIZZLE_64B
+__device__ __forceinline__ uint32_t swz64(uint32_t a) { return a ^ ((a >> 3) & 0x30u); }
+
+// window of one query at one level, shared by producer and sampler (same code, same result)
+struct Window {
+  int bx0, by0;   // first block column / row of the box (may lie outside the image)
+  int wide, tall; // 0/1: box is 2+wide blocks x 3+tall block rows
+  int fast;       // all taps inside such a box (false only for |coords| so large that fp32 spacing breaks the pattern)
+};
+
+template <int R, int kMode>
+__device__ __forceinline__ Window window_of(float cxl, float cyl, const Level16Dev& lv) {
+  constexpr int rd = 2 * R + 1;
+  const int x_lo = make_tap_fast(cxl, (float)(-R), lv.sm1x, lv.invx, lv.halfx, kMode).i0;
+  const int x_hi = make_tap_fast(cxl, (float)(rd - 1 - R), lv.sm1x, lv.invx, lv.halfx, kMode).i0 + 1;
+  const int y_lo = make_tap_fast(cyl, (float)(-R), lv.sm1y, lv.invy, lv.halfy, kMode).i0;
+  const int y_hi = make_tap_fast(cyl, (float)(rd - 1 - R), lv.sm1y, lv.invy, lv.halfy, kMode).i0 + 1;
+  Window w;
+  w.bx0 = x_lo >> 3;
+  w.by0 = y_lo >> 2;
+  const int nbx = (x_hi >> 3) - w.bx0 + 1, nby = (y_hi >> 2) - w.by0 + 1;
+  w.fast = (nbx >= 1) & (nbx <= 3) & (nby >= 1) & (nby <= 4);
+  w.wide = nbx > 2;
+  w.tall = nby > 3;
+  return w;
+}
+
+__device__ __forceinline__ float bf16_bits_to_float(uint32_t h) { return __uint_as_float(h << 16); }
+
+// rare path: straight from global memory, with bounds checks (zero padding)
+__device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img, int y, int x) {
+  if (x < 0 || y < 0 || x >= lv.W || y >= lv.H) return 0.0f;
+  const unsigned char* p = lv.data + img * lv.istride + ((long long)(y >> 2) * lv.bxs + (x >> 3)) * 64 + (y & 3) * 16 +
+                           (x & 7) * 2;
+  return bf16_bits_to_float(*reinterpret_cast<const unsigned short*>(p));
+}
+
+// One query's samples at one level for x taps [i_begin, i_end), from its slot.  Two code shapes:
+//   kChain = 2: x and y taps sit on consecutive pixels for every lane of the warp (the usual case): the window is
+//               a dense (rd+1) x (rd+1) patch and every pixel is loaded once (column carried from tap to tap)
+//   kChain = 0: floor flips of the coordinate round trip somewhere in the warp (integer coordinates: RAFT's
+//               first iteration): four loads per sample at the taps' own positions
+template <int R, int kMode, int kChain>
+__device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, const Tap (&ty)[2 * R + 1], float cxl,
+                                            const Level16Dev& lv, const Window& w, int i_begin, int i_end,
+                                            float* optr, long long N, bool live) {
+  constexpr int rd = 2 * R + 1;
+  const int rowpitch = bw * 64;   // bytes per block row of the box
+  // byte offset (before swizzling) of window row yy: whole block rows + row within the block
+  uint32_t rtop[rd], rbot[rd];
+  float fy[rd], sy[rd];
+#pragma unroll
+  for (int j = 0; j < rd; ++j) {
+    const int yy = ty[j].i0 - 4 * w.by0;
+    rtop[j] = slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16);
+    rbot[j] = slot_addr + (uint32_t)(((yy + 1) >> 2) * rowpitch + ((yy + 1) & 3) * 16);
+    fy[j] = ty[j].frac;
+    sy[j] = __fsub_rn(1.0f, fy[j]);
+  }
+  auto px = [&](uint32_t row, uint32_t col) -> float {
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz64(row + col)));
+    return bf16_bits_to_float(v);
+  };
+  auto combine = [&](float vnw, float vne, float vsw, float vse, float w_, float e_, float n_, float s_) {
+    // ATen's order (common.cuh bilinear_combine), with e = 1 - w and s = 1 - n hoisted
+    const float nw = __fmul_rn(s_, e_), ne = __fmul_rn(s_, w_), sw = __fmul_rn(n_, e_), se = __fmul_rn(n_, w_);
+    return __fmaf_rn(vse, se, __fmaf_rn(vsw, sw, __fmaf_rn(vne, ne, __fmul_rn(vnw, nw))));
+  };
+  if constexpr (kChain == 2) {
+    // dense patch: column c of the patch is pixel x_lo + c; carry the right column of tap i as the left of tap i+1
+    float left[rd + 1];
+    {
+      const Tap t = make_tap_fast(cxl, (float)(i_begin - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+      const int xx = t.i0 - 8 * w.bx0;
+      const uint32_t c = (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
+#pragma unroll
+      for (int j = 0; j < rd; ++j) left[j] = px(rtop[j], c);
+      left[rd] = px(rbot[rd - 1], c);
+    }
+#pragma unroll
+    for (int i = 0; i < rd; ++i) {
+      if (i < i_begin || i >= i_end) continue;
+      const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+      const int xx = t.i0 + 1 - 8 * w.bx0;
+      const uint32_t c = (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
+      const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
+      float right[rd + 1];
+#pragma unroll
+      for (int j = 0; j < rd; ++j) right[j] = px(rtop[j], c);
+      right[rd] = px(rbot[rd - 1], c);
+#pragma unroll
+      for (int j = 0; j < rd; ++j) {
+        const float v = combine(left[j], right[j], left[j + 1], right[j + 1], fx, ex, fy[j], sy[j]);
+        if (live) __stcs(optr + (long long)(i * rd + j) * N, v);
+      }
+#pragma unroll
+      for (int j = 0; j <= rd; ++j) left[j] = right[j];
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < rd; ++i) {
+      if (i < i_begin || i >= i_end) continue;
+      const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+      const int xx = t.i0 - 8 * w.bx0;
+      const uint32_t cl = (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
+      const uint32_t cr = (uint32_t)(((xx + 1) >> 3) * 64 + ((xx + 1) & 7) * 2);
+      const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
+#pragma unroll
+      for (int j = 0; j < rd; ++j) {
+        const float v = combine(px(rtop[j], cl), px(rtop[j], cr), px(rbot[j], cl), px(rbot[j], cr), fx, ex, fy[j], sy[j]);
+        if (live) __stcs(optr + (long long)(i * rd + j) * N, v);
+      }
+    }
+  }
+}
+
+// whole warp off the fast path (some lane's window does not fit a box): every lane samples from global memory
+template <int R, int kMode>
+__device__ __noinline__ void sample_unit_global(const Level16Dev& lv, long long img, float cxl, float cyl, int i_begin,
+                                                int i_end, float* optr, long long N) {
+  constexpr int rd = 2 * R + 1;
+  for (int i = i_begin; i < i_end; ++i) {
+    const Tap a = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+    for (int j = 0; j < rd; ++j) {
+      const Tap c = make_tap_fast(cyl, (float)(j - R), lv.sm1y, lv.invy, lv.halfy, kMode);
+      const float v = bilinear_combine(pixel16_global(lv, img, c.i0, a.i0), pixel16_global(lv, img, c.i0, a.i0 + 1),
+                                       pixel16_global(lv, img, c.i0 + 1, a.i0), pixel16_global(lv, img, c.i0 + 1, a.i0 + 1),
+                                       a.frac, c.frac);
+      __stcs(optr + (long long)(i * rd + j) * N, v);
+    }
+  }
+}
+
+template <int R, int kMode>
+__global__ void __launch_bounds__(kThreads16, 1)
+lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant__ Lookup16Maps maps) {
+  constexpr int rd = 2 * R + 1, rd2 = rd * rd;
+  constexpr int kChannels = kL * rd2;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const uint32_t smem_base = smem_u32(smem);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  auto full_bar = [&](int b) { return smem_base + kOffBars16 + b * 8; };
+  auto empty_bar = [&](int b) { return smem_base + kOffBars16 + (kBufs + b) * 8; };
+
+  if (threadIdx.x < kBufs) {
+    mbar_init(full_bar(threadIdx.x), 1);    // the producer's arrive.expect_tx (+ the bytes of its 32 boxes)
+    mbar_init(empty_bar(threadIdx.x), 2);   // lane 0 of both sampler warps of the level
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  const long long N = (long long)p.H * p.W;
+  const int n_tiles = (int)((p.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);   // tiles of this CTA
+
+  const bool producer = warp >= kSamplers16;
+  const int level = producer ? warp - kSamplers16 : warp >> 1;
+  const Level16Dev lv = p.lv[level];
+  const uint32_t my_slot = (uint32_t)slot_of(lane, level) * kSlot;
+
+  // tile k of this CTA -> (b, y, x0); 32-bit arithmetic only
+  auto tile_at = [&](int k, int& b, int& y, int& x0) {
+    const unsigned tile = blockIdx.x + (unsigned)k * gridDim.x;
+    const unsigned t2 = tile / (unsigned)p.tiles_x;
+    x0 = (int)(tile - t2 * (unsigned)p.tiles_x) * kTileQ;
+    b = (int)(t2 / (unsigned)p.H);
+    y = (int)(t2 - (unsigned)b * (unsigned)p.H);
+  };
+  auto load_coords = [&](int k, float& cx, float& cy) {
+    cx = cy = 0.0f;
+    if (k >= n_tiles) return;
+    int b, y, x0;
+    tile_at(k, b, y, x0);
+    const int x = x0 + lane;
+    if (x < p.W) {
+      const float* c = p.coords + ((long long)b * 2) * N + (long long)y * p.W + x;
+      cx = __ldg(c);
+      cy = __ldg(c + N);
+    }
+  };
+
+  float ncx, ncy;
+  load_coords(0, ncx, ncy);
+  for (int k = 0; k < n_tiles; ++k) {
+    const int u = k * kL + level;            // unit sequence number inside this CTA
+    const int buf = u % kBufs;
+    const uint32_t use = (uint32_t)(u / kBufs);
+    int b, y, x0;
+    tile_at(k, b, y, x0);
+    const int x = x0 + lane;
+    const bool live = x < p.W;
+    const float cx = ncx, cy = ncy;
+    load_coords(k + 1, ncx, ncy);            // one tile ahead
+    // core/corr.py:41  centroid / 2**i
+    const float cxl = __fmul_rn(cx, lv.inv_pow2), cyl = __fmul_rn(cy, lv.inv_pow2);
+    const Window w = window_of<R, kMode>(cxl, cyl, lv);
+    const long long img = (long long)b * N + (long long)y * p.W + x;
+    const uint32_t slot_addr = smem_base + buf * kBufBytes + my_slot;
+    const int bw = 2 + w.wide, bh = 3 + w.tall;
+
+    if (producer) {
+      const uint32_t bytes = (live && w.fast) ? (uint32_t)(bw * bh * 64) : 0u;
+      const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
+      mbar_wait_relaxed(empty_bar(buf), (use & 1u) ^ 1u, 1);
+      if (lane == 0) mbar_expect_tx(full_bar(buf), total);
+      __syncwarp();
+      if (bytes) {
+        // windows entirely outside the image are all zeros wherever the box sits: clamp far-away origins
+        const int bx = max(-8, min(w.bx0, lv.bxs + 8)), by = max(-8, min(w.by0, lv.bys + 8));
+        tma_load_4d(slot_addr, &maps.m[level][w.wide][w.tall], full_bar(buf), 0, bx, by, (int)img);
+      }
+    } else {
+      const int h = warp & 1;
+      const int i_begin = h ? (rd + 1) / 2 : 0, i_end = h ? rd : (rd + 1) / 2;
+      float* optr = p.out + ((long long)b * kChannels + level * rd2) * N + (long long)y * p.W + x;
+      Tap ty[rd];
+      bool chain = true;
+#pragma unroll
+      for (int j = 0; j < rd; ++j) {
+        ty[j] = make_tap_fast(cyl, (float)(j - R), lv.sm1y, lv.invy, lv.halfy, kMode);
+        if (j) chain &= ty[j].i0 == ty[j - 1].i0 + 1;
+      }
+      {
+        int prev = 0;
+#pragma unroll
+        for (int i = 0; i < rd; ++i) {
+          const int i0 = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode).i0;
+          if (i) chain &= i0 == prev + 1;
+          prev = i0;
+        }
+      }
+      const bool all_fast = __all_sync(0xffffffffu, w.fast || !live);
+      const bool all_chain = __all_sync(0xffffffffu, chain || !live);
+      mbar_wait(full_bar(buf), use & 1u, 2);
+      if (!all_fast) {
+        if (live) sample_unit_global<R, kMode>(lv, img, cxl, cyl, i_begin, i_end, optr, N);
+      } else if (all_chain) {
+        sample_unit<R, kMode, 2>(slot_addr, bw, ty, cxl, lv, w, i_begin, i_end, optr, N, live);
+      } else {
+        sample_unit<R, kMode, 0>(slot_addr, bw, ty, cxl, lv, w, i_begin, i_end, optr, N, live);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty_bar(buf));
+    }
+  }
+}
