@@ -42,6 +42,10 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
                     cudaStream_t stream);
 int launch_build_tc_noalloc(const float* f1, const float* f2, int B, int D, int H, int W, int L,
                             const raftcorr_level* levels, int precision, cudaStream_t stream);
+int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int W, int L,
+                      const raftcorr_level16* levels, void* ws, int64_t ws_bytes, cudaStream_t stream);
+int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coords, float* out, int B, int H, int W,
+                        int r, int mode, cudaStream_t stream);
 int64_t build_bwd_workspace_bytes(int B, int D, int H, int W);
 int launch_build_bwd(const raftcorr_level* glevels, int L, const float* f1, const float* f2,
                      float* g1, float* g2, int B, int D, int H, int W, void* ws, int64_t ws_bytes,
@@ -77,6 +81,24 @@ static int check_levels(const raftcorr_level* levels, int L, int H, int W, const
     RC_REQUIRE(levels[l].pitch >= levels[l].W &&
                    levels[l].image_stride >= levels[l].pitch * levels[l].H,
                "%s: levels[%d] pitch/image_stride too small", what, l);
+  }
+  return 0;
+}
+
+static int check_levels16(const raftcorr_level16* levels, int L, int H, int W, const char* what) {
+  RC_REQUIRE(levels != nullptr, "%s: levels is NULL", what);
+  RC_REQUIRE(L >= 1 && L <= RAFTCORR_MAX_LEVELS, "%s: num_levels=%d not in [1,%d]", what, L, RAFTCORR_MAX_LEVELS);
+  for (int l = 0; l < L; ++l) {
+    const raftcorr_level16& v = levels[l];
+    RC_REQUIRE(v.data != nullptr, "%s: levels[%d].data is NULL", what, l);
+    RC_REQUIRE(!(reinterpret_cast<uintptr_t>(v.data) & 63), "%s: levels[%d].data must be 64-byte aligned", what, l);
+    RC_REQUIRE(v.H == (H >> l) && v.W == (W >> l) && v.H >= 1 && v.W >= 1,
+               "%s: levels[%d] is %dx%d, expected %dx%d (avg_pool2d floors)", what, l, v.H, v.W, H >> l, W >> l);
+    RC_REQUIRE(v.blocks_x == (v.W + 7) / 8 && v.blocks_y == (v.H + 3) / 4,
+               "%s: levels[%d] block grid %dx%d does not match %dx%d pixels (use raftcorr_pyramid16_layout)", what, l,
+               v.blocks_x, v.blocks_y, v.W, v.H);
+    RC_REQUIRE(v.image_stride >= (int64_t)v.blocks_x * v.blocks_y * 64 && !(v.image_stride & 63),
+               "%s: levels[%d].image_stride must be a multiple of 64 and >= blocks_x*blocks_y*64", what, l);
   }
   return 0;
 }
@@ -160,6 +182,44 @@ int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B
   if (D % 8 != 0) return launch_build_fp32(fmap1, fmap2, B, D, H, W, num_levels, levels, (cudaStream_t)stream);
   return launch_build_tc_noalloc(fmap1, fmap2, B, D, H, W, num_levels, levels, precision,
                                  (cudaStream_t)stream);
+}
+
+int raftcorr_pyramid16_layout(int B, int H, int W, int num_levels, raftcorr_level16* levels,
+                              int64_t* bytes_per_level) {
+  RC_REQUIRE(levels && bytes_per_level, "pyramid16_layout: NULL output");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "pyramid16_layout: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(num_levels >= 1 && num_levels <= RAFTCORR_MAX_LEVELS, "pyramid16_layout: num_levels=%d", num_levels);
+  for (int l = 0; l < num_levels; ++l) {
+    const int Hl = H >> l, Wl = W >> l;
+    RC_REQUIRE(Hl >= 1 && Wl >= 1, "pyramid16_layout: level %d of %dx%d is empty", l, H, W);
+    levels[l].H = Hl;
+    levels[l].W = Wl;
+    levels[l].blocks_x = (Wl + 7) / 8;
+    levels[l].blocks_y = (Hl + 3) / 4;
+    levels[l].image_stride = (int64_t)levels[l].blocks_x * levels[l].blocks_y * 64;
+    bytes_per_level[l] = (int64_t)B * H * W * levels[l].image_stride;
+  }
+  return 0;
+}
+
+int raftcorr_build_pyramid16(const float* fmap1, const float* fmap2, int B, int D, int H, int W,
+                             int num_levels, const raftcorr_level16* levels, void* workspace,
+                             int64_t workspace_bytes, void* stream) {
+  RC_REQUIRE(fmap1 && fmap2, "build_pyramid16: fmap pointer is NULL");
+  RC_REQUIRE(B >= 0 && D >= 1 && H >= 1 && W >= 1, "build_pyramid16: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
+  RC_REQUIRE((long long)H * W <= (1 << 24), "build_pyramid16: fmap too large");
+  if (int rc = check_levels16(levels, num_levels, H, W, "build_pyramid16")) return rc;
+  return launch_build_tc16(fmap1, fmap2, B, D, H, W, num_levels, levels, workspace, workspace_bytes,
+                           (cudaStream_t)stream);
+}
+
+int raftcorr_lookup16_fwd(const raftcorr_level16* levels, int num_levels, const float* coords, float* out,
+                          int B, int H, int W, int radius, int coord_mode, void* stream) {
+  RC_REQUIRE(coords && out, "lookup16_fwd: coords/out is NULL");
+  RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "lookup16_fwd: bad sizes B=%d H=%d W=%d", B, H, W);
+  RC_REQUIRE(valid_mode(coord_mode), "lookup16_fwd: coord_mode=%d", coord_mode);
+  if (int rc = check_levels16(levels, num_levels, H, W, "lookup16_fwd")) return rc;
+  return launch_lookup16_fwd(levels, num_levels, coords, out, B, H, W, radius, coord_mode, (cudaStream_t)stream);
 }
 
 int raftcorr_lookup_fwd(const raftcorr_level* levels, int num_levels, const float* coords,

@@ -321,3 +321,128 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     }
   }
 }
+
+// Tensor maps depend only on (pointers, sizes, strides); RAFT calls the lookup once per refinement iteration on the
+// same pyramid and encoding 16 maps costs more host time than the kernel runs: keep the last few sets behind a
+// mutex (the library stays re-entrant under nn.DataParallel's one-thread-per-GPU calls).
+struct MapKey16 {
+  const void* data[kL];
+  long long istride[kL], bn;
+  int bxs[kL], bys[kL];
+};
+constexpr int kMapCache16 = 8;
+struct MapCache16 {
+  std::mutex mu;
+  MapKey16 keys[kMapCache16];
+  Lookup16Maps maps[kMapCache16];
+  unsigned long long stamp[kMapCache16] = {};
+  unsigned long long clock = 0;
+};
+MapCache16& map_cache16() {
+  static MapCache16 c;
+  return c;
+}
+
+template <int R, int kMode>
+int launch16(const Lookup16Params& p, const Lookup16Maps& maps, cudaStream_t stream) {
+  int dev = 0;
+  RC_CHECK_CUDA(cudaGetDevice(&dev));
+  static std::atomic<int> sm_count[64];  // per device: 0 = kernel attribute not set yet
+  int sms = (dev >= 0 && dev < 64) ? sm_count[dev].load(std::memory_order_acquire) : 0;
+  if (sms == 0) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(lookup16_kernel<R, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem16));
+    RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (dev >= 0 && dev < 64) sm_count[dev].store(sms, std::memory_order_release);
+  }
+  const int grid = (int)(p.tiles < sms ? p.tiles : sms);
+  lookup16_kernel<R, kMode><<<grid, kThreads16, kSmem16, stream>>>(p, maps);
+  RC_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coords, float* out, int B, int H, int W,
+                        int r, int mode, cudaStream_t stream) {
+  if (L != kL || (r != 3 && r != 4))
+    return fail(RAFTCORR_E_UNSUPPORTED, "lookup16_fwd: needs num_levels == 4 and radius 3 or 4 (got %d, %d)", L, r);
+  if (get_encode() == nullptr) return fail(RAFTCORR_E_DRIVER, "cuTensorMapEncodeTiled is not available from this driver");
+  const long long BN = (long long)B * H * W;
+  if (BN >= (1LL << 31)) return fail(RAFTCORR_E_UNSUPPORTED, "lookup16_fwd: B*H*W must be below 2^31");
+  Lookup16Params p;
+  MapKey16 key;
+  memset(&key, 0, sizeof(key));
+  key.bn = BN;
+  for (int l = 0; l < kL; ++l) {
+    const raftcorr_level16& s = levels[l];
+    Level16Dev& d = p.lv[l];
+    d.data = static_cast<const unsigned char*>(s.data);
+    d.H = s.H;
+    d.W = s.W;
+    d.bxs = s.blocks_x;
+    d.bys = s.blocks_y;
+    d.istride = s.image_stride;
+    d.sm1x = (float)(s.W - 1);
+    d.invx = 1.0f / d.sm1x;
+    d.halfx = d.sm1x / 2.0f;
+    d.sm1y = (float)(s.H - 1);
+    d.invy = 1.0f / d.sm1y;
+    d.halfy = d.sm1y / 2.0f;
+    d.inv_pow2 = 1.0f / (float)(1 << l);
+    key.data[l] = s.data;
+    key.istride[l] = s.image_stride;
+    key.bxs[l] = s.blocks_x;
+    key.bys[l] = s.blocks_y;
+  }
+  Lookup16Maps maps;
+  bool hit = false;
+  {
+    MapCache16& c = map_cache16();
+    std::lock_guard<std::mutex> g(c.mu);
+    for (int i = 0; i < kMapCache16 && !hit; ++i)
+      if (c.stamp[i] && memcmp(&c.keys[i], &key, sizeof(key)) == 0) {
+        c.stamp[i] = ++c.clock;
+        maps = c.maps[i];
+        hit = true;
+      }
+  }
+  if (!hit) {
+    for (int l = 0; l < kL; ++l) {
+      cuuint64_t dims[4] = {32, (cuuint64_t)levels[l].blocks_x, (cuuint64_t)levels[l].blocks_y, (cuuint64_t)BN};
+      cuuint64_t strides[3] = {64, (cuuint64_t)levels[l].blocks_x * 64, (cuuint64_t)levels[l].image_stride};
+      for (int wide = 0; wide < 2; ++wide)
+        for (int tall = 0; tall < 2; ++tall) {
+          cuuint32_t box[4] = {32, (cuuint32_t)(2 + wide), (cuuint32_t)(3 + tall), 1};
+          if (int rc = encode(&maps.m[l][wide][tall], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, levels[l].data, dims, strides,
+                              box, CU_TENSOR_MAP_SWIZZLE_64B, "lookup16 window", CU_TENSOR_MAP_L2_PROMOTION_NONE))
+            return rc;
+        }
+    }
+    MapCache16& c = map_cache16();
+    std::lock_guard<std::mutex> g(c.mu);
+    int victim = 0;
+    for (int i = 1; i < kMapCache16; ++i)
+      if (c.stamp[i] < c.stamp[victim]) victim = i;
+    c.keys[victim] = key;
+    c.maps[victim] = maps;
+    c.stamp[victim] = ++c.clock;
+  }
+  p.coords = coords;
+  p.out = out;
+  p.B = B;
+  p.H = H;
+  p.W = W;
+  p.tiles_x = (W + kTileQ - 1) / kTileQ;
+  p.tiles = (long long)B * H * p.tiles_x;
+  if (p.tiles == 0) return 0;
+  switch (mode * 8 + r) {
+    case RAFTCORR_COORD_ATEN_CPU * 8 + 4: return launch16<4, RAFTCORR_COORD_ATEN_CPU>(p, maps, stream);
+    case RAFTCORR_COORD_ATEN_CPU * 8 + 3: return launch16<3, RAFTCORR_COORD_ATEN_CPU>(p, maps, stream);
+    case RAFTCORR_COORD_ATEN_CUDA * 8 + 4: return launch16<4, RAFTCORR_COORD_ATEN_CUDA>(p, maps, stream);
+    case RAFTCORR_COORD_ATEN_CUDA * 8 + 3: return launch16<3, RAFTCORR_COORD_ATEN_CUDA>(p, maps, stream);
+    case RAFTCORR_COORD_DIRECT * 8 + 4: return launch16<4, RAFTCORR_COORD_DIRECT>(p, maps, stream);
+    default: return launch16<3, RAFTCORR_COORD_DIRECT>(p, maps, stream);
+  }
+}
+
+}  // namespace raftcorr

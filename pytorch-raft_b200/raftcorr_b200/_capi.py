@@ -28,6 +28,15 @@ class Level(ctypes.Structure):
 
 LevelArray = Level * MAX_LEVELS
 
+
+class Level16(ctypes.Structure):
+    """struct raftcorr_level16: bfloat16 pixels in 4x8 blocks of 64 bytes"""
+    _fields_ = [("data", ctypes.c_void_p), ("H", ctypes.c_int32), ("W", ctypes.c_int32),
+                ("blocks_x", ctypes.c_int32), ("blocks_y", ctypes.c_int32), ("image_stride", ctypes.c_int64)]
+
+
+Level16Array = Level16 * MAX_LEVELS
+
 #: every symbol include/raftcorr.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "raftcorr_version": (ctypes.c_int, []),
@@ -40,6 +49,12 @@ SIGNATURES = {
                                 ctypes.c_void_p]),
     "raftcorr_build_pyramid_noalloc": (ctypes.c_int, [c_float_p, c_float_p] + [ctypes.c_int] * 5 +
                                        [ctypes.POINTER(Level), ctypes.c_int, ctypes.c_void_p]),
+    "raftcorr_pyramid16_layout": (ctypes.c_int, [ctypes.c_int] * 4 + [ctypes.POINTER(Level16),
+                                                                    ctypes.POINTER(ctypes.c_int64)]),
+    "raftcorr_build_pyramid16": (ctypes.c_int, [c_float_p, c_float_p] + [ctypes.c_int] * 5 +
+                                 [ctypes.POINTER(Level16), ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "raftcorr_lookup16_fwd": (ctypes.c_int, [ctypes.POINTER(Level16), ctypes.c_int, c_float_p, c_float_p] +
+                              [ctypes.c_int] * 5 + [ctypes.c_void_p]),
     "raftcorr_lookup_fwd": (ctypes.c_int, [ctypes.POINTER(Level), ctypes.c_int, c_float_p, c_float_p] +
                             [ctypes.c_int] * 5 + [ctypes.c_void_p]),
     "raftcorr_lookup_fwd_nhwc": (ctypes.c_int, [ctypes.POINTER(Level), ctypes.c_int, c_float_p, c_float_p] +
