@@ -29,7 +29,7 @@ class CorrBlock:
     ``(B*H*W, 1, H_l, W_l)`` (strided views: rows are padded to 16 bytes for TMA)."""
 
     def __init__(self, fmap1, fmap2, num_levels=4, radius=4, *, precision=None, coord_mode=None,
-                 channels_last=False):
+                 channels_last=False, storage=None):
         self.num_levels = num_levels
         self.radius = radius
         self._coord_mode = ops.resolve_coord_mode(coord_mode)
@@ -38,13 +38,27 @@ class CorrBlock:
         self._channels_last = bool(channels_last)
         self._holder = {}
         self._token = None
+        self._views = None
         if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
+            # gradients flow through the fp32 pyramid (the format core/corr.py itself stores)
             self._token, *views = ops.BuildFn.apply(fmap1, fmap2, num_levels,
                                                     ops.resolve_precision(precision), self._holder)
-            self.corr_pyramid = list(views)
+            self._views = list(views)
         else:
-            self._holder["pyr"] = ops.build_pyramid(fmap1, fmap2, num_levels, precision)
-            self.corr_pyramid = self._holder["pyr"].views()
+            # inference: with the (default) bf16 arithmetic the pyramid is also STORED in bf16, in 64-byte blocks
+            # (storage='auto'; 'fp32' keeps the reference's format) - half the bytes to write and to look up
+            if self._channels_last and storage in (None, "auto"):
+                storage = "fp32"
+            self._holder["pyr"] = ops.build_pyramid(fmap1, fmap2, num_levels, precision, storage=storage,
+                                                    radius=radius)
+
+    @property
+    def corr_pyramid(self):
+        """core/corr.py:21-27's public list of (B*H*W, 1, H_l, W_l) float32 levels.  Views of the fp32 pyramid;
+        for the 16-bit pyramid a de-blocked, widened copy made on first access (RAFT itself never reads it)."""
+        if self._views is None:
+            self._views = self._holder["pyr"].views()
+        return self._views
 
     def __call__(self, coords):
         needs_graph = torch.is_grad_enabled() and (
@@ -66,13 +80,15 @@ class CorrBlock:
                                         (self._token is not None and self._token.requires_grad)):
             raise RuntimeError("lookup_conv1x1 is an inference path: call the block and the convolution separately "
                                "when gradients are needed")
+        if not isinstance(self._holder["pyr"], ops.Pyramid):
+            raise RuntimeError("lookup_conv1x1 reads the fp32 pyramid: construct the block with storage='fp32'")
         return ops.lookup_conv1x1(self._holder["pyr"], coords, self.radius, weight, bias, relu, self._coord_mode)
 
     @staticmethod
     def corr(fmap1, fmap2, *, precision=None):
         """core/corr.py:52-60: the all-pairs volume (B,H,W,1,H,W), scaled by 1/sqrt(D)."""
         B, D, H, W = fmap1.shape
-        pyr = ops.build_pyramid(fmap1, fmap2, 1, precision)
+        pyr = ops.build_pyramid(fmap1, fmap2, 1, precision, storage="fp32")
         return pyr.views()[0].reshape(B, H, W, 1, H, W)
 
 

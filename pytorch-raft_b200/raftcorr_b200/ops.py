@@ -14,7 +14,7 @@ import torch
 
 from . import _capi
 from ._capi import (COORD_ATEN_CPU, COORD_ATEN_CUDA, COORD_DIRECT, PREC_BF16, PREC_FP32, PREC_TF32,
-                    Level, LevelArray)
+                    Level, Level16Array, LevelArray)
 
 _PRECISIONS = {"fp32": PREC_FP32, "bf16": PREC_BF16, "tf32": PREC_TF32}
 _COORD_MODES = {"aten_cpu": COORD_ATEN_CPU, "aten_cuda": COORD_ATEN_CUDA, "direct": COORD_DIRECT}
@@ -91,9 +91,67 @@ class Pyramid:
         return [self.storage[l][:, :, : self.desc[l].W].unsqueeze(1) for l in range(self.num_levels)]
 
 
+class Pyramid16:
+    """Device storage of a correlation pyramid in 16 bits (include/raftcorr.h, raftcorr_level16): bfloat16
+    pixels in blocks of 4 rows x 8 columns, ``storage[l]`` indexed [image][block row][block col][row][col].
+    Half the bytes of ``Pyramid`` for the build to write and the lookup to read; inference only."""
+
+    def __init__(self, B: int, H: int, W: int, num_levels: int, device, zero: bool = False):
+        self.B, self.H, self.W, self.num_levels = B, H, W, num_levels
+        self.desc = Level16Array()
+        nbytes = (ctypes.c_int64 * _capi.MAX_LEVELS)()
+        _capi.check(_capi.lib().raftcorr_pyramid16_layout(B, H, W, num_levels, self.desc, nbytes),
+                    "raftcorr_pyramid16_layout")
+        alloc = torch.zeros if zero else torch.empty
+        self.storage: List[torch.Tensor] = []
+        for l in range(num_levels):
+            d = self.desc[l]
+            buf = alloc((B * H * W, d.blocks_y, d.blocks_x, 4, 8), dtype=torch.bfloat16, device=device)
+            d.data = buf.data_ptr()
+            self.storage.append(buf)
+
+    def dense(self, l: int) -> torch.Tensor:
+        """Level l de-blocked and widened: (B*H*W, H_l, W_l) float32 (a copy; layout conversion only)."""
+        d, s = self.desc[l], self.storage[l]
+        full = s.permute(0, 1, 3, 2, 4).reshape(s.shape[0], 4 * d.blocks_y, 8 * d.blocks_x)
+        return full[:, : d.H, : d.W].float()
+
+    def views(self) -> List[torch.Tensor]:
+        """(B*H*W, 1, H_l, W_l) float32 tensors, the shape core/corr.py:22-27 exposes (copies)."""
+        return [self.dense(l).unsqueeze(1) for l in range(self.num_levels)]
+
+    @classmethod
+    def from_dense(cls, levels: Sequence[torch.Tensor], B: int, H: int, W: int, device="cuda") -> "Pyramid16":
+        """Blocked bf16 copy of reference-shaped levels (B*H*W, 1, H_l, W_l) (rounded to bf16, padding zeroed)."""
+        pyr = cls(B, H, W, len(levels), device, zero=True)
+        for l, lv in enumerate(levels):
+            d = pyr.desc[l]
+            t = torch.as_tensor(lv, device=device).reshape(B * H * W, d.H, d.W).to(torch.bfloat16)
+            full = torch.zeros((B * H * W, 4 * d.blocks_y, 8 * d.blocks_x), dtype=torch.bfloat16, device=device)
+            full[:, : d.H, : d.W] = t
+            pyr.storage[l].copy_(full.reshape(B * H * W, d.blocks_y, 4, d.blocks_x, 8).permute(0, 1, 3, 2, 4))
+        return pyr
+
+
+def resolve_storage(storage, precision: int, D: int, num_levels: int, radius) -> str:
+    """'fp32' (row-major fp32, core/corr.py's own format, needed for gradients) or 'bf16' (blocked bfloat16).
+    'auto': 'bf16' whenever the bf16 arithmetic was asked for and the 16-bit kernels cover the case."""
+    if storage is None:
+        storage = os.environ.get("RAFTCORR_PYRAMID", "auto")
+    if storage not in ("auto", "fp32", "bf16"):
+        raise ValueError(f"pyramid storage must be 'auto', 'fp32' or 'bf16', got {storage!r}")
+    covered = precision == PREC_BF16 and D % 8 == 0 and num_levels == 4 and radius in (None, 3, 4)
+    if storage == "bf16" and not covered:
+        raise RuntimeError("16-bit pyramid storage needs precision='bf16', D % 8 == 0, num_levels == 4 and radius 3 or 4")
+    if storage == "auto":
+        storage = "bf16" if covered else "fp32"
+    return storage
+
+
 def build_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
-                  precision=None) -> Pyramid:
-    """core/corr.py:13-27 + 52-60 in one launch sequence (pack, tcgen05 GEMM + pooled epilogue)."""
+                  precision=None, storage="fp32", radius=None):
+    """core/corr.py:13-27 + 52-60 in one launch sequence (pack, tcgen05 GEMM + pooled epilogue).
+    Returns a ``Pyramid`` (fp32 rows) or, for storage 'bf16' / 'auto', a ``Pyramid16`` (blocked bfloat16)."""
     _require_cuda_f32(fmap1, "fmap1")
     _require_cuda_f32(fmap2, "fmap2")
     if fmap1.shape != fmap2.shape or fmap1.dim() != 4:
@@ -102,6 +160,16 @@ def build_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
     B, D, H, W = fmap1.shape
     prec = resolve_precision(precision)
     lib = _capi.lib()
+    if resolve_storage(storage, prec, D, num_levels, radius) == "bf16":
+        with torch.cuda.device(fmap1.device):
+            pyr16 = Pyramid16(B, H, W, num_levels, fmap1.device)
+            ws_bytes = int(lib.raftcorr_build_workspace_bytes(B, D, H, W, PREC_BF16))
+            ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=fmap1.device)
+            _capi.check(lib.raftcorr_build_pyramid16(fmap1.data_ptr(), fmap2.data_ptr(), B, D, H, W, num_levels,
+                                                     pyr16.desc, ws.data_ptr(), ws_bytes, _stream(fmap1)),
+                        "raftcorr_build_pyramid16")
+            ws.record_stream(torch.cuda.current_stream(fmap1.device))
+        return pyr16
     with torch.cuda.device(fmap1.device):
         pyr = Pyramid(B, H, W, num_levels, fmap1.device)
         ws_bytes = int(lib.raftcorr_build_workspace_bytes(B, D, H, W, prec))
@@ -123,6 +191,15 @@ def lookup(pyr: Pyramid, coords: torch.Tensor, radius: int, coord_mode=None, cha
     coords = coords.contiguous()
     rd = 2 * radius + 1
     C = pyr.num_levels * rd * rd
+    if isinstance(pyr, Pyramid16):
+        if channels_last:
+            raise RuntimeError("the channels-last lookup reads the fp32 pyramid: build it with storage='fp32'")
+        out = torch.empty((B, C, H, W), dtype=torch.float32, device=coords.device)
+        with _on_device(coords.device):
+            _capi.check(_capi.lib().raftcorr_lookup16_fwd(pyr.desc, pyr.num_levels, coords.data_ptr(), out.data_ptr(),
+                                                          B, H, W, radius, resolve_coord_mode(coord_mode),
+                                                          _stream(coords)), "raftcorr_lookup16_fwd")
+        return out
     if channels_last:
         out = torch.empty((B, H, W, C), dtype=torch.float32, device=coords.device)
         fn, name = _capi.lib().raftcorr_lookup_fwd_nhwc, "raftcorr_lookup_fwd_nhwc"
