@@ -17,7 +17,8 @@
 //               the 32 lanes are 32 consecutive x, so every store instruction is one full 128-byte line and
 //               the output never passes through shared memory
 //
-// Shared memory: 7 unit buffers x 32 slots x 896 B.  The 32 windows are walked in lock step, at the same
+// Shared memory: 8 unit buffers (a ring of two per level: an mbarrier's parity only tells apart neighbouring
+// phases, so every buffer must be filled and drained by the same warps use after use) x 32 slots x 896 B.  The 32 windows are walked in lock step, at the same
 // in-window offset more often than not, and TMA wants 128-byte aligned destinations, so unskewed slots would put
 // all lanes on one bank.  The boxes are therefore fetched with the 64-byte TMA swizzle (16-byte chunk index
 // bits 4-5 ^= address bits 7-8; measured layout: tools/probe/tma_swizzle_probe.cu — the 128-byte swizzle pads
@@ -42,7 +43,8 @@ constexpr int kL = RAFTCORR_MAX_LEVELS;           // the kernel is specialised f
 constexpr int kSamplers16 = 8;
 constexpr int kProducers16 = 4;
 constexpr int kThreads16 = (kSamplers16 + kProducers16) * 32;
-constexpr int kBufs = 7;
+constexpr int kDepth16 = 2;                        // unit buffers per level (each level runs its own ring)
+constexpr int kBufs = kL * kDepth16;
 constexpr int kSlot = 896;                         // 7 x 128 B >= the largest box (3 x 4 blocks = 768 B)
 constexpr int kBufBytes = 32 * kSlot;              // 28 KB: a multiple of 1024, so swizzle phases are slot-relative
 constexpr int kOffBars16 = kBufs * kBufBytes;
@@ -259,9 +261,8 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   float ncx, ncy;
   load_coords(0, ncx, ncy);
   for (int k = 0; k < n_tiles; ++k) {
-    const int u = k * kL + level;            // unit sequence number inside this CTA
-    const int buf = u % kBufs;
-    const uint32_t use = (uint32_t)(u / kBufs);
+    const int buf = level * kDepth16 + (k % kDepth16);   // this level's ring
+    const uint32_t use = (uint32_t)(k / kDepth16);
     int b, y, x0;
     tile_at(k, b, y, x0);
     const int x = x0 + lane;

@@ -100,7 +100,8 @@ def test_build16_overwrites_stale_padding():
 
 
 @pytest.mark.parametrize("kind", KINDS)
-@pytest.mark.parametrize("case", [(1, 16, 18, 4), (2, 17, 23, 3), (1, 46, 62, 4), (3, 9, 33, 4), (1, 16, 95, 3), (1, 16, 16, 4)])
+@pytest.mark.parametrize("case", [(1, 16, 18, 4), (2, 17, 23, 3), (1, 46, 62, 4), (3, 9, 33, 4), (1, 16, 95, 3), (1, 16, 16, 4),
+                                  (6, 40, 70, 4)])   # the last one: several tiles per CTA, the rings wrap
 def test_lookup16_bit_exact_against_oracle(case, kind):
     B, H, W, r = case
     gen = torch.Generator().manual_seed(H * 100 + W + r)
@@ -111,8 +112,10 @@ def test_lookup16_bit_exact_against_oracle(case, kind):
     out = ops.lookup(pyr, c.cuda(), r, "aten_cpu").cpu().numpy()
     ref = oracle.lookup(stored, c.numpy(), r)
     assert out.shape == ref.shape
+    # (a level with H_l == 1 or W_l == 1 divides by zero in the reference, utils.py:61-62: NaN there, in both)
+    assert np.array_equal(np.isnan(out), np.isnan(ref)), (case, kind)
     assert np.array_equal(out == 0, ref == 0), (case, kind)
-    assert np.array_equal(out, ref), (case, kind, np.abs(out - ref).max())
+    assert np.array_equal(np.nan_to_num(out, nan=0.0), np.nan_to_num(ref, nan=0.0)), (case, kind)
 
 
 @pytest.mark.parametrize("mode", ["aten_cuda", "direct"])
