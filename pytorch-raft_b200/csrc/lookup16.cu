@@ -87,13 +87,7 @@ struct Window {
   int fast;       // all taps inside such a box (false only for |coords| so large that fp32 spacing breaks the pattern)
 };
 
-template <int R, int kMode>
-__device__ __forceinline__ Window window_of(float cxl, float cyl, const Level16Dev& lv) {
-  constexpr int rd = 2 * R + 1;
-  const int x_lo = make_tap_fast(cxl, (float)(-R), lv.sm1x, lv.invx, lv.halfx, kMode).i0;
-  const int x_hi = make_tap_fast(cxl, (float)(rd - 1 - R), lv.sm1x, lv.invx, lv.halfx, kMode).i0 + 1;
-  const int y_lo = make_tap_fast(cyl, (float)(-R), lv.sm1y, lv.invy, lv.halfy, kMode).i0;
-  const int y_hi = make_tap_fast(cyl, (float)(rd - 1 - R), lv.sm1y, lv.invy, lv.halfy, kMode).i0 + 1;
+__device__ __forceinline__ Window window_from(int x_lo, int x_hi, int y_lo, int y_hi) {
   Window w;
   w.bx0 = x_lo >> 3;
   w.by0 = y_lo >> 2;
@@ -102,6 +96,16 @@ __device__ __forceinline__ Window window_of(float cxl, float cyl, const Level16D
   w.wide = nbx > 2;
   w.tall = nby > 3;
   return w;
+}
+// first and last tap decide the box (taps are monotone in their offset)
+template <int R, int kMode>
+__device__ __forceinline__ Window window_of(float cxl, float cyl, const Level16Dev& lv) {
+  constexpr int rd = 2 * R + 1;
+  const int x_lo = make_tap_fast(cxl, (float)(-R), lv.sm1x, lv.invx, lv.halfx, kMode).i0;
+  const int x_hi = make_tap_fast(cxl, (float)(rd - 1 - R), lv.sm1x, lv.invx, lv.halfx, kMode).i0 + 1;
+  const int y_lo = make_tap_fast(cyl, (float)(-R), lv.sm1y, lv.invy, lv.halfy, kMode).i0;
+  const int y_hi = make_tap_fast(cyl, (float)(rd - 1 - R), lv.sm1y, lv.invy, lv.halfy, kMode).i0 + 1;
+  return window_from(x_lo, x_hi, y_lo, y_hi);
 }
 
 __device__ __forceinline__ float bf16_bits_to_float(uint32_t h) { return __uint_as_float(h << 16); }
@@ -114,28 +118,19 @@ __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img
   return bf16_bits_to_float(*reinterpret_cast<const unsigned short*>(p));
 }
 
-// One query's samples at one level for x taps [i_begin, i_end), from its slot.  Two code shapes:
-//   kChain = 2: x and y taps sit on consecutive pixels for every lane of the warp (the usual case): the window is
-//               a dense (rd+1) x (rd+1) patch and every pixel is loaded once (column carried from tap to tap)
-//   kChain = 0: floor flips of the coordinate round trip somewhere in the warp (integer coordinates: RAFT's
-//               first iteration): four loads per sample at the taps' own positions
-template <int R, int kMode, int kChain>
-__device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, const Tap (&ty)[2 * R + 1], float cxl,
-                                            const Level16Dev& lv, const Window& w, int i_begin, int i_end,
-                                            float* optr, long long N, bool live) {
+// One query's (2r+1)^2 samples at one level, from its slot.  Two code shapes:
+//   kChain = true : x and y taps sit on consecutive pixels for every lane of the warp (the usual case): the
+//                   window is a dense (rd+1) x (rd+1) patch and every pixel is loaded once (the right-hand column
+//                   of x tap i is carried over as the left-hand column of tap i+1)
+//   kChain = false: floor flips of the coordinate round trip somewhere in the warp (integer coordinates: RAFT's
+//                   first iteration): four loads per sample at the taps' own positions
+template <int R, bool kChain>
+__device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0, int by0, const Tap (&tx)[2 * R + 1],
+                                            const Tap (&ty)[2 * R + 1], float* optr, long long N, bool live) {
   constexpr int rd = 2 * R + 1;
   const int rowpitch = bw * 64;   // bytes per block row of the box
-  // byte offset (before swizzling) of window row yy: whole block rows + row within the block
-  uint32_t rtop[rd], rbot[rd];
-  float fy[rd], sy[rd];
-#pragma unroll
-  for (int j = 0; j < rd; ++j) {
-    const int yy = ty[j].i0 - 4 * w.by0;
-    rtop[j] = slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16);
-    rbot[j] = slot_addr + (uint32_t)(((yy + 1) >> 2) * rowpitch + ((yy + 1) & 3) * 16);
-    fy[j] = ty[j].frac;
-    sy[j] = __fsub_rn(1.0f, fy[j]);
-  }
+  auto row_off = [&](int yy) { return slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16); };
+  auto col_off = [&](int xx) { return (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2); };
   auto px = [&](uint32_t row, uint32_t col) -> float {
     unsigned short v;
     asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz64(row + col)));
@@ -146,49 +141,57 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, const Ta
     const float nw = __fmul_rn(s_, e_), ne = __fmul_rn(s_, w_), sw = __fmul_rn(n_, e_), se = __fmul_rn(n_, w_);
     return __fmaf_rn(vse, se, __fmaf_rn(vsw, sw, __fmaf_rn(vne, ne, __fmul_rn(vnw, nw))));
   };
-  if constexpr (kChain == 2) {
-    // dense patch: column c of the patch is pixel x_lo + c; carry the right column of tap i as the left of tap i+1
-    float left[rd + 1];
-    {
-      const Tap t = make_tap_fast(cxl, (float)(i_begin - R), lv.sm1x, lv.invx, lv.halfx, kMode);
-      const int xx = t.i0 - 8 * w.bx0;
-      const uint32_t c = (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
+  float fy[rd], sy[rd];
 #pragma unroll
-      for (int j = 0; j < rd; ++j) left[j] = px(rtop[j], c);
-      left[rd] = px(rbot[rd - 1], c);
+  for (int j = 0; j < rd; ++j) {
+    fy[j] = ty[j].frac;
+    sy[j] = __fsub_rn(1.0f, fy[j]);
+  }
+  float* o = optr;
+  if constexpr (kChain) {
+    uint32_t rows[rd + 1];
+    const int yy0 = ty[0].i0 - 4 * by0, xx0 = tx[0].i0 - 8 * bx0;
+#pragma unroll
+    for (int r = 0; r <= rd; ++r) rows[r] = row_off(yy0 + r);
+    float left[rd + 1], right[rd + 1];
+    {
+      const uint32_t c = col_off(xx0);
+#pragma unroll
+      for (int r = 0; r <= rd; ++r) left[r] = px(rows[r], c);
     }
 #pragma unroll
     for (int i = 0; i < rd; ++i) {
-      if (i < i_begin || i >= i_end) continue;
-      const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
-      const int xx = t.i0 + 1 - 8 * w.bx0;
-      const uint32_t c = (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
-      const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
-      float right[rd + 1];
+      const uint32_t c = col_off(xx0 + i + 1);
+      const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
 #pragma unroll
-      for (int j = 0; j < rd; ++j) right[j] = px(rtop[j], c);
-      right[rd] = px(rbot[rd - 1], c);
+      for (int r = 0; r <= rd; ++r) right[r] = px(rows[r], c);
 #pragma unroll
       for (int j = 0; j < rd; ++j) {
         const float v = combine(left[j], right[j], left[j + 1], right[j + 1], fx, ex, fy[j], sy[j]);
-        if (live) __stcs(optr + (long long)(i * rd + j) * N, v);
+        if (live) __stcs(o, v);
+        o += N;
       }
 #pragma unroll
-      for (int j = 0; j <= rd; ++j) left[j] = right[j];
+      for (int r = 0; r <= rd; ++r) left[r] = right[r];
     }
   } else {
+    uint32_t rtop[rd], rbot[rd];
+#pragma unroll
+    for (int j = 0; j < rd; ++j) {
+      const int yy = ty[j].i0 - 4 * by0;
+      rtop[j] = row_off(yy);
+      rbot[j] = row_off(yy + 1);
+    }
 #pragma unroll
     for (int i = 0; i < rd; ++i) {
-      if (i < i_begin || i >= i_end) continue;
-      const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
-      const int xx = t.i0 - 8 * w.bx0;
-      const uint32_t cl = (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
-      const uint32_t cr = (uint32_t)(((xx + 1) >> 3) * 64 + ((xx + 1) & 7) * 2);
-      const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
+      const int xx = tx[i].i0 - 8 * bx0;
+      const uint32_t cl = col_off(xx), cr = col_off(xx + 1);
+      const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
 #pragma unroll
       for (int j = 0; j < rd; ++j) {
         const float v = combine(px(rtop[j], cl), px(rtop[j], cr), px(rbot[j], cl), px(rbot[j], cr), fx, ex, fy[j], sy[j]);
-        if (live) __stcs(optr + (long long)(i * rd + j) * N, v);
+        if (live) __stcs(o, v);
+        o += N;
       }
     }
   }
@@ -196,10 +199,10 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, const Ta
 
 // whole warp off the fast path (some lane's window does not fit a box): every lane samples from global memory
 template <int R, int kMode>
-__device__ __noinline__ void sample_unit_global(const Level16Dev& lv, long long img, float cxl, float cyl, int i_begin,
-                                                int i_end, float* optr, long long N) {
+__device__ __noinline__ void sample_unit_global(const Level16Dev& lv, long long img, float cxl, float cyl, float* optr,
+                                                long long N) {
   constexpr int rd = 2 * R + 1;
-  for (int i = i_begin; i < i_end; ++i) {
+  for (int i = 0; i < rd; ++i) {
     const Tap a = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
     for (int j = 0; j < rd; ++j) {
       const Tap c = make_tap_fast(cyl, (float)(j - R), lv.sm1y, lv.invy, lv.halfy, kMode);
@@ -224,7 +227,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
 
   if (threadIdx.x < kBufs) {
     mbar_init(full_bar(threadIdx.x), 1);    // the producer's arrive.expect_tx (+ the bytes of its 32 boxes)
-    mbar_init(empty_bar(threadIdx.x), 2);   // lane 0 of both sampler warps of the level
+    mbar_init(empty_bar(threadIdx.x), 1);   // lane 0 of the sampler warp that owns the buffer
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -258,9 +261,11 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     }
   };
 
+  // a producer walks every tile of its level; the level's two sampler warps take alternate tiles (one buffer each)
+  const int k_step = producer ? 1 : kDepth16;
   float ncx, ncy;
-  load_coords(0, ncx, ncy);
-  for (int k = 0; k < n_tiles; ++k) {
+  load_coords(producer ? 0 : (warp & 1), ncx, ncy);
+  for (int k = producer ? 0 : (warp & 1); k < n_tiles; k += k_step) {
     const int buf = level * kDepth16 + (k % kDepth16);   // this level's ring
     const uint32_t use = (uint32_t)(k / kDepth16);
     int b, y, x0;
@@ -268,15 +273,15 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     const int x = x0 + lane;
     const bool live = x < p.W;
     const float cx = ncx, cy = ncy;
-    load_coords(k + 1, ncx, ncy);            // one tile ahead
+    load_coords(k + k_step, ncx, ncy);       // one unit ahead
     // core/corr.py:41  centroid / 2**i
     const float cxl = __fmul_rn(cx, lv.inv_pow2), cyl = __fmul_rn(cy, lv.inv_pow2);
-    const Window w = window_of<R, kMode>(cxl, cyl, lv);
     const long long img = (long long)b * N + (long long)y * p.W + x;
     const uint32_t slot_addr = smem_base + buf * kBufBytes + my_slot;
-    const int bw = 2 + w.wide, bh = 3 + w.tall;
 
     if (producer) {
+      const Window w = window_of<R, kMode>(cxl, cyl, lv);
+      const int bw = 2 + w.wide, bh = 3 + w.tall;
       const uint32_t bytes = (live && w.fast) ? (uint32_t)(bw * bh * 64) : 0u;
       const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
       mbar_wait_relaxed(empty_bar(buf), (use & 1u) ^ 1u, 1);
@@ -288,34 +293,26 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
         tma_load_4d(slot_addr, &maps.m[level][w.wide][w.tall], full_bar(buf), 0, bx, by, (int)img);
       }
     } else {
-      const int h = warp & 1;
-      const int i_begin = h ? (rd + 1) / 2 : 0, i_end = h ? rd : (rd + 1) / 2;
       float* optr = p.out + ((long long)b * kChannels + level * rd2) * N + (long long)y * p.W + x;
-      Tap ty[rd];
+      Tap tx[rd], ty[rd];
       bool chain = true;
 #pragma unroll
       for (int j = 0; j < rd; ++j) {
         ty[j] = make_tap_fast(cyl, (float)(j - R), lv.sm1y, lv.invy, lv.halfy, kMode);
-        if (j) chain &= ty[j].i0 == ty[j - 1].i0 + 1;
+        tx[j] = make_tap_fast(cxl, (float)(j - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+        if (j) chain &= (ty[j].i0 == ty[j - 1].i0 + 1) & (tx[j].i0 == tx[j - 1].i0 + 1);
       }
-      {
-        int prev = 0;
-#pragma unroll
-        for (int i = 0; i < rd; ++i) {
-          const int i0 = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode).i0;
-          if (i) chain &= i0 == prev + 1;
-          prev = i0;
-        }
-      }
+      const Window w = window_from(tx[0].i0, tx[rd - 1].i0 + 1, ty[0].i0, ty[rd - 1].i0 + 1);   // = the producer's
+      const int bw = 2 + w.wide;
       const bool all_fast = __all_sync(0xffffffffu, w.fast || !live);
       const bool all_chain = __all_sync(0xffffffffu, chain || !live);
       mbar_wait(full_bar(buf), use & 1u, 2);
       if (!all_fast) {
-        if (live) sample_unit_global<R, kMode>(lv, img, cxl, cyl, i_begin, i_end, optr, N);
+        if (live) sample_unit_global<R, kMode>(lv, img, cxl, cyl, optr, N);
       } else if (all_chain) {
-        sample_unit<R, kMode, 2>(slot_addr, bw, ty, cxl, lv, w, i_begin, i_end, optr, N, live);
+        sample_unit<R, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
       } else {
-        sample_unit<R, kMode, 0>(slot_addr, bw, ty, cxl, lv, w, i_begin, i_end, optr, N, live);
+        sample_unit<R, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_bar(buf));
