@@ -12,7 +12,8 @@
 //               lane (cp.async.bulk.tensor.4d over the level's (64-byte block, blocks_x, blocks_y, image)
 //               tensor: {2,3} x {3,4} whole blocks; out-of-image blocks arrive as zeros = grid_sample's zero
 //               padding) into the lane's slot of a unit buffer, all 32 boxes on one mbarrier
-//   samplers  = 8 warps, a pair per level (the pair splits the x taps): lane q forms its query's (2r+1)^2
+//   samplers  = 16 warps, per level a pair for each of its two unit buffers (the pair splits the x taps, the two
+//               pairs take alternate tiles): lane q forms its query's (2r+1)^2
 //               samples out of its own slot and stores them straight to the NCHW output — for a fixed channel
 //               the 32 lanes are 32 consecutive x, so every store instruction is one full 128-byte line and
 //               the output never passes through shared memory
@@ -40,7 +41,7 @@ namespace {
 using namespace lk;
 
 constexpr int kL = RAFTCORR_MAX_LEVELS;           // the kernel is specialised for the 4-level pyramid
-constexpr int kSamplers16 = 8;
+constexpr int kSamplers16 = 16;                    // per level: 2 buffers x 2 warps (the pair splits the x taps)
 constexpr int kProducers16 = 4;
 constexpr int kThreads16 = (kSamplers16 + kProducers16) * 32;
 constexpr int kDepth16 = 2;                        // unit buffers per level (each level runs its own ring)
@@ -124,10 +125,10 @@ __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img
 //                   of x tap i is carried over as the left-hand column of tap i+1)
 //   kChain = false: floor flips of the coordinate round trip somewhere in the warp (integer coordinates: RAFT's
 //                   first iteration): four loads per sample at the taps' own positions
-template <int R, bool kChain>
+template <int R, bool kChain, int kIB, int kIE, bool kAllLive>
 __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0, int by0, const Tap (&tx)[2 * R + 1],
                                             const Tap (&ty)[2 * R + 1], float* optr, long long N, bool live) {
-  constexpr int rd = 2 * R + 1;
+  constexpr int rd = 2 * R + 1;   // this warp forms the samples of x taps kIB .. kIE-1
   const int rowpitch = bw * 64;   // bytes per block row of the box
   auto row_off = [&](int yy) { return slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16); };
   auto col_off = [&](int xx) { return (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2); };
@@ -147,7 +148,7 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
     fy[j] = ty[j].frac;
     sy[j] = __fsub_rn(1.0f, fy[j]);
   }
-  float* o = optr;
+  float* o = optr + (long long)(kIB * rd) * N;
   if constexpr (kChain) {
     uint32_t rows[rd + 1];
     const int yy0 = ty[0].i0 - 4 * by0, xx0 = tx[0].i0 - 8 * bx0;
@@ -155,12 +156,12 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
     for (int r = 0; r <= rd; ++r) rows[r] = row_off(yy0 + r);
     float left[rd + 1], right[rd + 1];
     {
-      const uint32_t c = col_off(xx0);
+      const uint32_t c = col_off(xx0 + kIB);
 #pragma unroll
       for (int r = 0; r <= rd; ++r) left[r] = px(rows[r], c);
     }
 #pragma unroll
-    for (int i = 0; i < rd; ++i) {
+    for (int i = kIB; i < kIE; ++i) {
       const uint32_t c = col_off(xx0 + i + 1);
       const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
 #pragma unroll
@@ -168,7 +169,7 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
 #pragma unroll
       for (int j = 0; j < rd; ++j) {
         const float v = combine(left[j], right[j], left[j + 1], right[j + 1], fx, ex, fy[j], sy[j]);
-        if (live) __stcs(o, v);
+        if (kAllLive || live) __stcs(o, v);
         o += N;
       }
 #pragma unroll
@@ -183,14 +184,14 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
       rbot[j] = row_off(yy + 1);
     }
 #pragma unroll
-    for (int i = 0; i < rd; ++i) {
+    for (int i = kIB; i < kIE; ++i) {
       const int xx = tx[i].i0 - 8 * bx0;
       const uint32_t cl = col_off(xx), cr = col_off(xx + 1);
       const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
 #pragma unroll
       for (int j = 0; j < rd; ++j) {
         const float v = combine(px(rtop[j], cl), px(rtop[j], cr), px(rbot[j], cl), px(rbot[j], cr), fx, ex, fy[j], sy[j]);
-        if (live) __stcs(o, v);
+        if (kAllLive || live) __stcs(o, v);
         o += N;
       }
     }
@@ -199,10 +200,10 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
 
 // whole warp off the fast path (some lane's window does not fit a box): every lane samples from global memory
 template <int R, int kMode>
-__device__ __noinline__ void sample_unit_global(const Level16Dev& lv, long long img, float cxl, float cyl, float* optr,
-                                                long long N) {
+__device__ __noinline__ void sample_unit_global(const Level16Dev& lv, long long img, float cxl, float cyl, int i_begin,
+                                                int i_end, float* optr, long long N) {
   constexpr int rd = 2 * R + 1;
-  for (int i = 0; i < rd; ++i) {
+  for (int i = i_begin; i < i_end; ++i) {
     const Tap a = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
     for (int j = 0; j < rd; ++j) {
       const Tap c = make_tap_fast(cyl, (float)(j - R), lv.sm1y, lv.invy, lv.halfy, kMode);
@@ -227,7 +228,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
 
   if (threadIdx.x < kBufs) {
     mbar_init(full_bar(threadIdx.x), 1);    // the producer's arrive.expect_tx (+ the bytes of its 32 boxes)
-    mbar_init(empty_bar(threadIdx.x), 1);   // lane 0 of the sampler warp that owns the buffer
+    mbar_init(empty_bar(threadIdx.x), 2);   // lane 0 of the two sampler warps that share the buffer
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -236,7 +237,8 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   const int n_tiles = (int)((p.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);   // tiles of this CTA
 
   const bool producer = warp >= kSamplers16;
-  const int level = producer ? warp - kSamplers16 : warp >> 1;
+  const int level = producer ? warp - kSamplers16 : warp >> 2;
+  const int my_buf = (warp >> 1) & 1;      // samplers: which of the level's two buffers this warp pair drains
   const Level16Dev lv = p.lv[level];
   const uint32_t my_slot = (uint32_t)slot_of(lane, level) * kSlot;
 
@@ -261,38 +263,77 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     }
   };
 
-  // a producer walks every tile of its level; the level's two sampler warps take alternate tiles (one buffer each)
-  const int k_step = producer ? 1 : kDepth16;
-  float ncx, ncy;
-  load_coords(producer ? 0 : (warp & 1), ncx, ncy);
-  for (int k = producer ? 0 : (warp & 1); k < n_tiles; k += k_step) {
-    const int buf = level * kDepth16 + (k % kDepth16);   // this level's ring
-    const uint32_t use = (uint32_t)(k / kDepth16);
-    int b, y, x0;
-    tile_at(k, b, y, x0);
-    const int x = x0 + lane;
-    const bool live = x < p.W;
-    const float cx = ncx, cy = ncy;
-    load_coords(k + k_step, ncx, ncy);       // one unit ahead
-    // core/corr.py:41  centroid / 2**i
-    const float cxl = __fmul_rn(cx, lv.inv_pow2), cyl = __fmul_rn(cy, lv.inv_pow2);
-    const long long img = (long long)b * N + (long long)y * p.W + x;
-    const uint32_t slot_addr = smem_base + buf * kBufBytes + my_slot;
-
-    if (producer) {
-      const Window w = window_of<R, kMode>(cxl, cyl, lv);
-      const int bw = 2 + w.wide, bh = 3 + w.tall;
-      const uint32_t bytes = (live && w.fast) ? (uint32_t)(bw * bh * 64) : 0u;
+  if (producer) {
+    // One producer warp per level walks every tile.  The level's ring holds only two units, so a fill can start
+    // only when a sampler pair has drained a buffer; to keep that fill short the boxes of the NEXT tile are
+    // requested into L2 (cp.async.bulk.prefetch.tensor) while this warp would otherwise sit on the empty barrier.
+    struct Unit {
+      Window w;
+      long long img;
+      bool live;
+    };
+    auto unit_of = [&](int k, float cx, float cy) {
+      Unit u;
+      int b, y, x0;
+      tile_at(k, b, y, x0);
+      const int x = x0 + lane;
+      u.live = x < p.W;
+      u.img = (long long)b * N + (long long)y * p.W + x;
+      u.w = window_of<R, kMode>(__fmul_rn(cx, lv.inv_pow2), __fmul_rn(cy, lv.inv_pow2), lv);   // corr.py:41
+      return u;
+    };
+    float c0x, c0y, c1x, c1y, c2x, c2y;     // coordinates of tiles k, k+1, k+2 (loaded two tiles ahead)
+    load_coords(0, c0x, c0y);
+    load_coords(1, c1x, c1y);
+    Unit cur = unit_of(0, c0x, c0y);
+    for (int k = 0; k < n_tiles; ++k) {
+      load_coords(k + 2, c2x, c2y);
+      const int buf = level * kDepth16 + (k % kDepth16);
+      const uint32_t use = (uint32_t)(k / kDepth16);
+      Unit nxt = cur;
+      if (k + 1 < n_tiles) {
+        nxt = unit_of(k + 1, c1x, c1y);
+        if (nxt.live && nxt.w.fast) {
+          const int bx = max(-8, min(nxt.w.bx0, lv.bxs + 8)), by = max(-8, min(nxt.w.by0, lv.bys + 8));
+          tma_prefetch_4d(&maps.m[level][nxt.w.wide][nxt.w.tall], 0, bx, by, (int)nxt.img);
+        }
+      }
+      const int bw = 2 + cur.w.wide, bh = 3 + cur.w.tall;
+      const uint32_t bytes = (cur.live && cur.w.fast) ? (uint32_t)(bw * bh * 64) : 0u;
       const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
       mbar_wait_relaxed(empty_bar(buf), (use & 1u) ^ 1u, 1);
       if (lane == 0) mbar_expect_tx(full_bar(buf), total);
       __syncwarp();
       if (bytes) {
         // windows entirely outside the image are all zeros wherever the box sits: clamp far-away origins
-        const int bx = max(-8, min(w.bx0, lv.bxs + 8)), by = max(-8, min(w.by0, lv.bys + 8));
-        tma_load_4d(slot_addr, &maps.m[level][w.wide][w.tall], full_bar(buf), 0, bx, by, (int)img);
+        const int bx = max(-8, min(cur.w.bx0, lv.bxs + 8)), by = max(-8, min(cur.w.by0, lv.bys + 8));
+        tma_load_4d(smem_base + buf * kBufBytes + my_slot, &maps.m[level][cur.w.wide][cur.w.tall], full_bar(buf), 0, bx,
+                    by, (int)cur.img);
       }
-    } else {
+      cur = nxt;
+      c1x = c2x;
+      c1y = c2y;
+    }
+    return;
+  }
+
+  // samplers: the level's two warp pairs take alternate tiles (one buffer each)
+  float ncx, ncy;
+  load_coords(my_buf, ncx, ncy);
+  for (int k = my_buf; k < n_tiles; k += kDepth16) {
+    const int buf = level * kDepth16 + my_buf;
+    const uint32_t use = (uint32_t)(k / kDepth16);
+    int b, y, x0;
+    tile_at(k, b, y, x0);
+    const int x = x0 + lane;
+    const bool live = x < p.W;
+    const float cx = ncx, cy = ncy;
+    load_coords(k + kDepth16, ncx, ncy);     // one unit ahead
+    // core/corr.py:41  centroid / 2**i
+    const float cxl = __fmul_rn(cx, lv.inv_pow2), cyl = __fmul_rn(cy, lv.inv_pow2);
+    const long long img = (long long)b * N + (long long)y * p.W + x;
+    const uint32_t slot_addr = smem_base + buf * kBufBytes + my_slot;
+    {
       float* optr = p.out + ((long long)b * kChannels + level * rd2) * N + (long long)y * p.W + x;
       Tap tx[rd], ty[rd];
       bool chain = true;
@@ -306,13 +347,21 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
       const int bw = 2 + w.wide;
       const bool all_fast = __all_sync(0xffffffffu, w.fast || !live);
       const bool all_chain = __all_sync(0xffffffffu, chain || !live);
+      const bool all_live = __all_sync(0xffffffffu, live);
+      constexpr int kMid = (rd + 1) / 2;     // the pair splits the x taps: [0, kMid) and [kMid, rd)
+      const int h = warp & 1;
       mbar_wait(full_bar(buf), use & 1u, 2);
       if (!all_fast) {
-        if (live) sample_unit_global<R, kMode>(lv, img, cxl, cyl, optr, N);
+        if (live) sample_unit_global<R, kMode>(lv, img, cxl, cyl, h ? kMid : 0, h ? rd : kMid, optr, N);
+      } else if (all_chain && all_live) {
+        if (h == 0) sample_unit<R, true, 0, kMid, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
+        else sample_unit<R, true, kMid, rd, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
       } else if (all_chain) {
-        sample_unit<R, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
+        if (h == 0) sample_unit<R, true, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
+        else sample_unit<R, true, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
       } else {
-        sample_unit<R, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
+        if (h == 0) sample_unit<R, false, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
+        else sample_unit<R, false, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_bar(buf));
