@@ -8,24 +8,25 @@
 // Here a LANE owns a query:
 //
 //   unit      = 32 consecutive-x queries of one fmap row at ONE pyramid level (4 units per tile)
-//   producers = 4 warps, one per level: lane q derives its query's window, the warp issues one TMA box per
-//               lane (cp.async.bulk.tensor.4d over the level's (64-byte block, blocks_x, blocks_y, image)
-//               tensor: {2,3} x {3,4} whole blocks; out-of-image blocks arrive as zeros = grid_sample's zero
-//               padding) into the lane's slot of a unit buffer, all 32 boxes on one mbarrier
-//   samplers  = 16 warps, per level a pair for each of its two unit buffers (the pair splits the x taps, the two
-//               pairs take alternate tiles): lane q forms its query's (2r+1)^2
-//               samples out of its own slot and stores them straight to the NCHW output — for a fixed channel
-//               the 32 lanes are 32 consecutive x, so every store instruction is one full 128-byte line and
-//               the output never passes through shared memory
+//   warp pair = owns one unit buffer and walks every other tile of its level (8 pairs: 4 levels x 2).  Lane q
+//               derives its query's window; the pair requests one TMA box per lane (cp.async.bulk.tensor.4d over
+//               the level's (64-byte block, blocks_x, blocks_y, image) tensor: {2,3} x {3,4} whole blocks;
+//               out-of-image blocks arrive as zeros = grid_sample's zero padding; each warp issues 16 of them,
+//               no producer warp: one warp can issue a box only every ~140 cycles) into the lane's slot, all 32
+//               boxes on one mbarrier.  When they have landed, lane q forms its query's (2r+1)^2 samples out of
+//               its own slot (the two warps split the x taps) and stores them straight to the NCHW output — for
+//               a fixed channel the 32 lanes are 32 consecutive x, so every store instruction is one full
+//               128-byte line and the output never passes through shared memory.  Then the pair refills its
+//               buffer with its next unit; the other seven pairs keep the SM busy meanwhile.
 //
-// Shared memory: 8 unit buffers (a ring of two per level: an mbarrier's parity only tells apart neighbouring
-// phases, so every buffer must be filled and drained by the same warps use after use) x 32 slots x 896 B.  The 32 windows are walked in lock step, at the same
+// Shared memory: 8 unit buffers x 32 slots x 896 B.  The 32 windows are walked in lock step, at the same
 // in-window offset more often than not, and TMA wants 128-byte aligned destinations, so unskewed slots would put
 // all lanes on one bank.  The boxes are therefore fetched with the 64-byte TMA swizzle (16-byte chunk index
 // bits 4-5 ^= address bits 7-8; measured layout: tools/probe/tma_swizzle_probe.cu — the 128-byte swizzle pads
 // every 64-byte block to a 128-byte row and would double the footprint) at a slot pitch that is an odd multiple
 // of 128 B: four skew classes.  The slot order puts lanes whose windows start one pixel apart at their level
 // into the same class, so that class mates fall on different words.
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -41,15 +42,14 @@ namespace {
 using namespace lk;
 
 constexpr int kL = RAFTCORR_MAX_LEVELS;           // the kernel is specialised for the 4-level pyramid
-constexpr int kSamplers16 = 16;                    // per level: 2 buffers x 2 warps (the pair splits the x taps)
-constexpr int kProducers16 = 4;
-constexpr int kThreads16 = (kSamplers16 + kProducers16) * 32;
+constexpr int kWarps16 = 16;                       // per level: 2 unit buffers x a pair of warps
+constexpr int kThreads16 = kWarps16 * 32;
 constexpr int kDepth16 = 2;                        // unit buffers per level (each level runs its own ring)
 constexpr int kBufs = kL * kDepth16;
 constexpr int kSlot = 896;                         // 7 x 128 B >= the largest box (3 x 4 blocks = 768 B)
 constexpr int kBufBytes = 32 * kSlot;              // 28 KB: a multiple of 1024, so swizzle phases are slot-relative
 constexpr int kOffBars16 = kBufs * kBufBytes;
-constexpr int kSmem16 = kOffBars16 + 2 * kBufs * 8;
+constexpr int kSmem16 = kOffBars16 + kBufs * 8;
 
 struct Level16Dev {
   const unsigned char* data;
@@ -64,6 +64,7 @@ struct Lookup16Params {
   float* out;
   int B, H, W, tiles_x;
   long long tiles;
+  int debug;   // development switches (RAFTCORR_L16_DEBUG): 1 = samplers skip the sampling, 2 = producer prefetches into L2
 };
 
 // box shapes: [level][wide: 2 or 3 blocks][tall: 3 or 4 block rows]
@@ -220,15 +221,14 @@ __global__ void __launch_bounds__(kThreads16, 1)
 lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant__ Lookup16Maps maps) {
   constexpr int rd = 2 * R + 1, rd2 = rd * rd;
   constexpr int kChannels = kL * rd2;
+  constexpr int kMid = (rd + 1) / 2;     // a pair splits the x taps: [0, kMid) and [kMid, rd)
   extern __shared__ __align__(1024) unsigned char smem[];
   const uint32_t smem_base = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   auto full_bar = [&](int b) { return smem_base + kOffBars16 + b * 8; };
-  auto empty_bar = [&](int b) { return smem_base + kOffBars16 + (kBufs + b) * 8; };
 
   if (threadIdx.x < kBufs) {
-    mbar_init(full_bar(threadIdx.x), 1);    // the producer's arrive.expect_tx (+ the bytes of its 32 boxes)
-    mbar_init(empty_bar(threadIdx.x), 2);   // lane 0 of the two sampler warps that share the buffer
+    mbar_init(full_bar(threadIdx.x), 2);    // one arrive.expect_tx per warp of the pair (+ the bytes of its 16 boxes)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -236,136 +236,108 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   const long long N = (long long)p.H * p.W;
   const int n_tiles = (int)((p.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);   // tiles of this CTA
 
-  const bool producer = warp >= kSamplers16;
-  const int level = producer ? warp - kSamplers16 : warp >> 2;
-  const int my_buf = (warp >> 1) & 1;      // samplers: which of the level's two buffers this warp pair drains
+  // warp pair = one unit buffer: pairs 2l, 2l+1 belong to level l and take alternate tiles
+  const int pair = warp >> 1, h = warp & 1;
+  const int level = pair >> 1, first = pair & 1;
   const Level16Dev lv = p.lv[level];
-  const uint32_t my_slot = (uint32_t)slot_of(lane, level) * kSlot;
+  const uint32_t slot_addr = smem_base + pair * kBufBytes + (uint32_t)slot_of(lane, level) * kSlot;
+  const uint32_t bar = full_bar(pair);
 
-  // tile k of this CTA -> (b, y, x0); 32-bit arithmetic only
-  auto tile_at = [&](int k, int& b, int& y, int& x0) {
-    const unsigned tile = blockIdx.x + (unsigned)k * gridDim.x;
+  struct Unit {
+    float cxl, cyl;      // core/corr.py:41  centroid / 2**i
+    long long img;
+    float* optr;
+    bool live;
+  };
+  auto unit_at = [&](int k, float cx, float cy) {
+    Unit u;
+    const unsigned tile = blockIdx.x + (unsigned)k * gridDim.x;       // 32-bit arithmetic only
     const unsigned t2 = tile / (unsigned)p.tiles_x;
-    x0 = (int)(tile - t2 * (unsigned)p.tiles_x) * kTileQ;
-    b = (int)(t2 / (unsigned)p.H);
-    y = (int)(t2 - (unsigned)b * (unsigned)p.H);
+    const int x = (int)(tile - t2 * (unsigned)p.tiles_x) * kTileQ + lane;
+    const int b = (int)(t2 / (unsigned)p.H);
+    const int y = (int)(t2 - (unsigned)b * (unsigned)p.H);
+    u.live = x < p.W;
+    u.img = (long long)b * N + (long long)y * p.W + x;
+    u.optr = p.out + ((long long)b * kChannels + level * rd2) * N + (long long)y * p.W + x;
+    u.cxl = __fmul_rn(cx, lv.inv_pow2);
+    u.cyl = __fmul_rn(cy, lv.inv_pow2);
+    return u;
   };
   auto load_coords = [&](int k, float& cx, float& cy) {
     cx = cy = 0.0f;
     if (k >= n_tiles) return;
-    int b, y, x0;
-    tile_at(k, b, y, x0);
-    const int x = x0 + lane;
+    const unsigned tile = blockIdx.x + (unsigned)k * gridDim.x;
+    const unsigned t2 = tile / (unsigned)p.tiles_x;
+    const int x = (int)(tile - t2 * (unsigned)p.tiles_x) * kTileQ + lane;
     if (x < p.W) {
-      const float* c = p.coords + ((long long)b * 2) * N + (long long)y * p.W + x;
+      const unsigned b = t2 / (unsigned)p.H;
+      const float* c = p.coords + (long long)(t2 + b * (unsigned)p.H) * p.W + x;   // (b*2*H + y) * W + x
       cx = __ldg(c);
       cy = __ldg(c + N);
     }
   };
-
-  if (producer) {
-    // One producer warp per level walks every tile.  The level's ring holds only two units, so a fill can start
-    // only when a sampler pair has drained a buffer; to keep that fill short the boxes of the NEXT tile are
-    // requested into L2 (cp.async.bulk.prefetch.tensor) while this warp would otherwise sit on the empty barrier.
-    struct Unit {
-      Window w;
-      long long img;
-      bool live;
-    };
-    auto unit_of = [&](int k, float cx, float cy) {
-      Unit u;
-      int b, y, x0;
-      tile_at(k, b, y, x0);
-      const int x = x0 + lane;
-      u.live = x < p.W;
-      u.img = (long long)b * N + (long long)y * p.W + x;
-      u.w = window_of<R, kMode>(__fmul_rn(cx, lv.inv_pow2), __fmul_rn(cy, lv.inv_pow2), lv);   // corr.py:41
-      return u;
-    };
-    float c0x, c0y, c1x, c1y, c2x, c2y;     // coordinates of tiles k, k+1, k+2 (loaded two tiles ahead)
-    load_coords(0, c0x, c0y);
-    load_coords(1, c1x, c1y);
-    Unit cur = unit_of(0, c0x, c0y);
-    for (int k = 0; k < n_tiles; ++k) {
-      load_coords(k + 2, c2x, c2y);
-      const int buf = level * kDepth16 + (k % kDepth16);
-      const uint32_t use = (uint32_t)(k / kDepth16);
-      Unit nxt = cur;
-      if (k + 1 < n_tiles) {
-        nxt = unit_of(k + 1, c1x, c1y);
-        if (nxt.live && nxt.w.fast) {
-          const int bx = max(-8, min(nxt.w.bx0, lv.bxs + 8)), by = max(-8, min(nxt.w.by0, lv.bys + 8));
-          tma_prefetch_4d(&maps.m[level][nxt.w.wide][nxt.w.tall], 0, bx, by, (int)nxt.img);
-        }
-      }
-      const int bw = 2 + cur.w.wide, bh = 3 + cur.w.tall;
-      const uint32_t bytes = (cur.live && cur.w.fast) ? (uint32_t)(bw * bh * 64) : 0u;
-      const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
-      mbar_wait_relaxed(empty_bar(buf), (use & 1u) ^ 1u, 1);
-      if (lane == 0) mbar_expect_tx(full_bar(buf), total);
-      __syncwarp();
-      if (bytes) {
-        // windows entirely outside the image are all zeros wherever the box sits: clamp far-away origins
-        const int bx = max(-8, min(cur.w.bx0, lv.bxs + 8)), by = max(-8, min(cur.w.by0, lv.bys + 8));
-        tma_load_4d(smem_base + buf * kBufBytes + my_slot, &maps.m[level][cur.w.wide][cur.w.tall], full_bar(buf), 0, bx,
-                    by, (int)cur.img);
-      }
-      cur = nxt;
-      c1x = c2x;
-      c1y = c2y;
+  // this warp requests the boxes of lanes 16h .. 16h+15 of the pair's next unit
+  auto issue = [&](const Unit& u) {
+    const Window w = window_of<R, kMode>(u.cxl, u.cyl, lv);
+    const int bw = 2 + w.wide, bh = 3 + w.tall;
+    const uint32_t bytes = (u.live && w.fast && (lane >> 4) == h) ? (uint32_t)(bw * bh * 64) : 0u;
+    const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
+    if (lane == 0) mbar_expect_tx(bar, total);
+    __syncwarp();
+    if (bytes) {
+      // windows entirely outside the image are all zeros wherever the box sits: clamp far-away origins
+      const int bx = max(-8, min(w.bx0, lv.bxs + 8)), by = max(-8, min(w.by0, lv.bys + 8));
+      tma_load_4d(slot_addr, &maps.m[level][w.wide][w.tall], bar, 0, bx, by, (int)u.img);
     }
-    return;
-  }
+  };
 
-  // samplers: the level's two warp pairs take alternate tiles (one buffer each)
   float ncx, ncy;
-  load_coords(my_buf, ncx, ncy);
-  for (int k = my_buf; k < n_tiles; k += kDepth16) {
-    const int buf = level * kDepth16 + my_buf;
-    const uint32_t use = (uint32_t)(k / kDepth16);
-    int b, y, x0;
-    tile_at(k, b, y, x0);
-    const int x = x0 + lane;
-    const bool live = x < p.W;
-    const float cx = ncx, cy = ncy;
-    load_coords(k + kDepth16, ncx, ncy);     // one unit ahead
-    // core/corr.py:41  centroid / 2**i
-    const float cxl = __fmul_rn(cx, lv.inv_pow2), cyl = __fmul_rn(cy, lv.inv_pow2);
-    const long long img = (long long)b * N + (long long)y * p.W + x;
-    const uint32_t slot_addr = smem_base + buf * kBufBytes + my_slot;
-    {
-      float* optr = p.out + ((long long)b * kChannels + level * rd2) * N + (long long)y * p.W + x;
-      Tap tx[rd], ty[rd];
-      bool chain = true;
+  load_coords(first, ncx, ncy);
+  if (first >= n_tiles) return;
+  Unit cur = unit_at(first, ncx, ncy);
+  issue(cur);
+  load_coords(first + kDepth16, ncx, ncy);
+  uint32_t phase = 0;
+  for (int k = first; k < n_tiles; k += kDepth16) {
+    const bool more = k + kDepth16 < n_tiles;
+    Unit nxt = cur;
+    if (more) nxt = unit_at(k + kDepth16, ncx, ncy);
+    load_coords(k + 2 * kDepth16, ncx, ncy);           // two units ahead
+    Tap tx[rd], ty[rd];
+    bool chain = true;
 #pragma unroll
-      for (int j = 0; j < rd; ++j) {
-        ty[j] = make_tap_fast(cyl, (float)(j - R), lv.sm1y, lv.invy, lv.halfy, kMode);
-        tx[j] = make_tap_fast(cxl, (float)(j - R), lv.sm1x, lv.invx, lv.halfx, kMode);
-        if (j) chain &= (ty[j].i0 == ty[j - 1].i0 + 1) & (tx[j].i0 == tx[j - 1].i0 + 1);
-      }
-      const Window w = window_from(tx[0].i0, tx[rd - 1].i0 + 1, ty[0].i0, ty[rd - 1].i0 + 1);   // = the producer's
-      const int bw = 2 + w.wide;
-      const bool all_fast = __all_sync(0xffffffffu, w.fast || !live);
-      const bool all_chain = __all_sync(0xffffffffu, chain || !live);
-      const bool all_live = __all_sync(0xffffffffu, live);
-      constexpr int kMid = (rd + 1) / 2;     // the pair splits the x taps: [0, kMid) and [kMid, rd)
-      const int h = warp & 1;
-      mbar_wait(full_bar(buf), use & 1u, 2);
-      if (!all_fast) {
-        if (live) sample_unit_global<R, kMode>(lv, img, cxl, cyl, h ? kMid : 0, h ? rd : kMid, optr, N);
-      } else if (all_chain && all_live) {
-        if (h == 0) sample_unit<R, true, 0, kMid, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
-        else sample_unit<R, true, kMid, rd, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
-      } else if (all_chain) {
-        if (h == 0) sample_unit<R, true, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
-        else sample_unit<R, true, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
-      } else {
-        if (h == 0) sample_unit<R, false, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
-        else sample_unit<R, false, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, optr, N, live);
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(empty_bar(buf));
+    for (int j = 0; j < rd; ++j) {
+      ty[j] = make_tap_fast(cur.cyl, (float)(j - R), lv.sm1y, lv.invy, lv.halfy, kMode);
+      tx[j] = make_tap_fast(cur.cxl, (float)(j - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+      if (j) chain &= (ty[j].i0 == ty[j - 1].i0 + 1) & (tx[j].i0 == tx[j - 1].i0 + 1);
     }
+    const Window w = window_from(tx[0].i0, tx[rd - 1].i0 + 1, ty[0].i0, ty[rd - 1].i0 + 1);   // = what issue() used
+    const int bw = 2 + w.wide;
+    const bool live = cur.live;
+    const bool all_fast = __all_sync(0xffffffffu, w.fast || !live);
+    const bool all_chain = __all_sync(0xffffffffu, chain || !live);
+    const bool all_live = __all_sync(0xffffffffu, live);
+    mbar_wait(bar, phase, 2);
+    phase ^= 1u;
+    if (p.debug & 1) {
+    } else if (!all_fast) {
+      if (live) sample_unit_global<R, kMode>(lv, cur.img, cur.cxl, cur.cyl, h ? kMid : 0, h ? rd : kMid, cur.optr, N);
+    } else if (all_chain && all_live) {
+      if (h == 0) sample_unit<R, true, 0, kMid, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      else sample_unit<R, true, kMid, rd, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+    } else if (all_chain) {
+      if (h == 0) sample_unit<R, true, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      else sample_unit<R, true, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+    } else {
+      if (h == 0) sample_unit<R, false, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      else sample_unit<R, false, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+    }
+    if (more) {
+      // both warps of the pair are done reading the buffer before either refills it
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
+      issue(nxt);
+    }
+    cur = nxt;
   }
 }
 
@@ -476,6 +448,10 @@ int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coor
   }
   p.coords = coords;
   p.out = out;
+  {
+    const char* dbg = getenv("RAFTCORR_L16_DEBUG");
+    p.debug = dbg ? atoi(dbg) : 0;
+  }
   p.B = B;
   p.H = H;
   p.W = W;
