@@ -126,9 +126,10 @@ __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img
 //                   of x tap i is carried over as the left-hand column of tap i+1)
 //   kChain = false: floor flips of the coordinate round trip somewhere in the warp (integer coordinates: RAFT's
 //                   first iteration): four loads per sample at the taps' own positions
-template <int R, bool kChain, int kIB, int kIE, bool kAllLive>
+template <int R, bool kChain, int kIB, int kIE, bool kAllLive, typename Between>
 __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0, int by0, const Tap (&tx)[2 * R + 1],
-                                            const Tap (&ty)[2 * R + 1], float* optr, long long N, bool live) {
+                                            const Tap (&ty)[2 * R + 1], float* optr, long long N, bool live,
+                                            Between&& between) {
   constexpr int rd = 2 * R + 1;   // this warp forms the samples of x taps kIB .. kIE-1
   const int rowpitch = bw * 64;   // bytes per block row of the box
   auto row_off = [&](int yy) { return slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16); };
@@ -151,30 +152,34 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
   }
   float* o = optr + (long long)(kIB * rd) * N;
   if constexpr (kChain) {
-    uint32_t rows[rd + 1];
-    const int yy0 = ty[0].i0 - 4 * by0, xx0 = tx[0].i0 - 8 * bx0;
-#pragma unroll
-    for (int r = 0; r <= rd; ++r) rows[r] = row_off(yy0 + r);
-    float left[rd + 1], right[rd + 1];
+    // Phase 1: the whole (rd+1) x (kIE-kIB+1) patch this warp needs goes into registers; then between() hands the
+    // buffer back (the pair refills it with its next unit) and phase 2 — arithmetic and stores, most of the time —
+    // runs while those boxes are in flight.
+    constexpr int kCols = kIE - kIB + 1;
+    float pxl[kCols][rd + 1];
     {
-      const uint32_t c = col_off(xx0 + kIB);
+      uint32_t rows[rd + 1];
+      const int yy0 = ty[0].i0 - 4 * by0, xx0 = tx[0].i0 - 8 * bx0;
 #pragma unroll
-      for (int r = 0; r <= rd; ++r) left[r] = px(rows[r], c);
+      for (int r = 0; r <= rd; ++r) rows[r] = row_off(yy0 + r);
+#pragma unroll
+      for (int c = 0; c < kCols; ++c) {
+        const uint32_t co = col_off(xx0 + kIB + c);
+#pragma unroll
+        for (int r = 0; r <= rd; ++r) pxl[c][r] = px(rows[r], co);
+      }
     }
+    between();
 #pragma unroll
     for (int i = kIB; i < kIE; ++i) {
-      const uint32_t c = col_off(xx0 + i + 1);
       const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
 #pragma unroll
-      for (int r = 0; r <= rd; ++r) right[r] = px(rows[r], c);
-#pragma unroll
       for (int j = 0; j < rd; ++j) {
-        const float v = combine(left[j], right[j], left[j + 1], right[j + 1], fx, ex, fy[j], sy[j]);
+        const float v = combine(pxl[i - kIB][j], pxl[i - kIB + 1][j], pxl[i - kIB][j + 1], pxl[i - kIB + 1][j + 1], fx, ex,
+                                fy[j], sy[j]);
         if (kAllLive || live) __stcs(o, v);
         o += N;
       }
-#pragma unroll
-      for (int r = 0; r <= rd; ++r) left[r] = right[r];
     }
   } else {
     uint32_t rtop[rd], rbot[rd];
@@ -196,6 +201,7 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
         o += N;
       }
     }
+    between();
   }
 }
 
@@ -295,6 +301,14 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   load_coords(first, ncx, ncy);
   if (first >= n_tiles) return;
   Unit cur = unit_at(first, ncx, ncy);
+  // All pairs take the same time per unit, so pairs that start together stay in lock step: every pair waits for
+  // its boxes at the same moment and every pair samples at the same moment, and the SM alternates between idle and
+  // oversubscribed.  Start half of them late (debug bits 8..: delay in units of 256 ns) so that one half samples
+  // while the other half's boxes are in flight.
+  if (first) {
+    const unsigned delay = (unsigned)(p.debug >> 8) * 256u;
+    for (unsigned t = 0; t < delay; t += 256u) __nanosleep(256);
+  }
   issue(cur);
   load_coords(first + kDepth16, ncx, ncy);
   uint32_t phase = 0;
@@ -319,23 +333,27 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     const bool all_live = __all_sync(0xffffffffu, live);
     mbar_wait(bar, phase, 2);
     phase ^= 1u;
+    // hand the buffer back: both warps of the pair are done reading it before either refills it
+    auto refill = [&]() {
+      if (more) {
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
+        issue(nxt);
+      }
+    };
     if (p.debug & 1) {
+      refill();
     } else if (!all_fast) {
       if (live) sample_unit_global<R, kMode>(lv, cur.img, cur.cxl, cur.cyl, h ? kMid : 0, h ? rd : kMid, cur.optr, N);
+      refill();
     } else if (all_chain && all_live) {
-      if (h == 0) sample_unit<R, true, 0, kMid, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
-      else sample_unit<R, true, kMid, rd, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      if (h == 0) sample_unit<R, true, 0, kMid, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
+      else sample_unit<R, true, kMid, rd, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
     } else if (all_chain) {
-      if (h == 0) sample_unit<R, true, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
-      else sample_unit<R, true, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      if (h == 0) sample_unit<R, true, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
+      else sample_unit<R, true, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
     } else {
-      if (h == 0) sample_unit<R, false, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
-      else sample_unit<R, false, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
-    }
-    if (more) {
-      // both warps of the pair are done reading the buffer before either refills it
-      asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
-      issue(nxt);
+      if (h == 0) sample_unit<R, false, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
+      else sample_unit<R, false, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
     }
     cur = nxt;
   }
