@@ -64,7 +64,7 @@ struct Lookup16Params {
   float* out;
   int B, H, W, tiles_x;
   long long tiles;
-  int debug;   // development switches (RAFTCORR_L16_DEBUG): 1 = samplers skip the sampling, 2 = producer prefetches into L2
+  int debug;   // development switches (RAFTCORR_L16_DEBUG): bit 0 = skip the sampling (fill path only); bits 8.. = start skew
 };
 
 // box shapes: [level][wide: 2 or 3 blocks][tall: 3 or 4 block rows]
@@ -302,12 +302,11 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   if (first >= n_tiles) return;
   Unit cur = unit_at(first, ncx, ncy);
   // All pairs take the same time per unit, so pairs that start together stay in lock step: every pair waits for
-  // its boxes at the same moment and every pair samples at the same moment, and the SM alternates between idle and
-  // oversubscribed.  Start half of them late (debug bits 8..: delay in units of 256 ns) so that one half samples
-  // while the other half's boxes are in flight.
+  // its boxes at the same moment and every pair samples at the same moment.  Half of them start one microsecond
+  // late (measured best; RAFTCORR_L16_DEBUG bits 8.. override it in units of 256 ns, 255 = none).
   if (first) {
-    const unsigned delay = (unsigned)(p.debug >> 8) * 256u;
-    for (unsigned t = 0; t < delay; t += 256u) __nanosleep(256);
+    const unsigned steps = (p.debug >> 8) ? (unsigned)(p.debug >> 8) : 4u;
+    for (unsigned t = 0; t < steps && steps != 255u; ++t) __nanosleep(256);
   }
   issue(cur);
   load_coords(first + kDepth16, ncx, ncy);
