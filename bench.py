@@ -56,7 +56,10 @@ METRIC = "RAFT frame-pairs/s @440x1024 12 iters; corr lookup HBM GB/s vs peak"
 UNIT = "frame-pairs/s"
 IMG_H, IMG_W, ITERS, BATCH_PER_GPU = 440, 1024, 12, 8
 RADIUS, LEVELS = 4, 4
-LOOKUP_BYTES_PER_QUERY = LEVELS * (2 * RADIUS + 2) ** 2 * 4 + 8 + LEVELS * (2 * RADIUS + 1) ** 2 * 4  # 2904
+# 4 levels x (2r+2)^2 window pixels read + 8 B of coordinates + 4 x (2r+1)^2 fp32 samples written:
+# 2904 B per query with an fp32 pyramid, 2104 B with the 16-bit pyramid
+def lookup_bytes_per_query(pixel_bytes: int) -> int:
+    return LEVELS * (2 * RADIUS + 2) ** 2 * pixel_bytes + 8 + LEVELS * (2 * RADIUS + 1) ** 2 * 4
 
 
 def measured_peaks():
@@ -67,20 +70,63 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic_per_launch(channels_last: bool):
-    """dram read+write bytes per lookup launch from the committed ncu --set full capture of the kernel variant
-    this run uses (NCHW or channels-last output)."""
+def git_blob_sha1(path: str):
+    import hashlib
+    try:
+        data = open(path, "rb").read()
+    except OSError:
+        return None
+    return hashlib.sha1(b"blob %d\0" % len(data) + data).hexdigest()
+
+
+def ncu_traffic_per_launch(kernel_key: str):
+    """dram read+write bytes per launch of the named lookup kernel from the committed ncu --set full capture
+    (profiles/lookup_traffic.json).  Every entry records the git blob hash of the kernel's source file at capture
+    time; a capture of an older version of the kernel is not reported (null)."""
     path = os.path.join(ROOT, "profiles", "lookup_traffic.json")
-    if os.path.exists(path):
-        try:
-            d = json.load(open(path))
-            if d.get("workload") == "cfg2_b8_55x128":
-                if channels_last:
-                    return float(d["channels_last"]["dram_bytes_per_launch"]) if "channels_last" in d else None
-                return float(d["dram_bytes_per_launch"])
-        except Exception:
-            pass
-    return None
+    try:
+        entry = json.load(open(path))["kernels"][kernel_key]
+        if entry.get("workload") != "cfg2_b8_55x128":
+            return None
+        if entry.get("source_blob") != git_blob_sha1(os.path.join(PKG, "csrc", entry["source_file"])):
+            return None
+        return float(entry["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
+def measure_tf32_peak(dev, seconds: float = 1.5):
+    """Dense TF32 peak on this GPU, measured the way MEASURED_PEAKS.json measures bf16: torch.matmul 8192^3 with
+    allow_tf32 (cuBLAS), best of 10 (burst) and back to back for `seconds` (sustained).  SURVEY.md 8(d)."""
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        n = 8192
+        a = torch.randn(n, n, device=dev)
+        b = torch.randn(n, n, device=dev)
+        flops = 2.0 * n ** 3
+        for _ in range(3):
+            a @ b
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        reps = max(int(seconds * 1e3 / best), 10)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            a @ b
+        e1.record()
+        torch.cuda.synchronize()
+        sustained = e0.elapsed_time(e1) / reps
+        return {"tf32_tflops": flops / best / 1e9, "tf32_tflops_sustained": flops / sustained / 1e9,
+                "how": f"torch.matmul fp32 8192^3 with allow_tf32: best of 10 (burst), {reps} back to back (sustained)"}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
 
 
 class ClockSampler:

@@ -33,3 +33,16 @@ def rel_max(a, ref):
     """max|a-ref| / max|ref| — the normalisation SURVEY.md §8(d) prescribes."""
     a, ref = np.asarray(a, dtype=np.float64), np.asarray(ref, dtype=np.float64)
     return float(np.abs(a - ref).max() / max(np.abs(ref).max(), 1e-30))
+
+
+def expected_zero_mask(block, coords, radius, ref):
+    """Which outputs must be exactly zero.  For the fp32 pyramid that is the reference's own zero pattern (all of
+    it zero padding: fp32 sums do not cancel by accident).  With 16-bit storage two neighbouring pixels can round
+    to exact opposites, so a tap at a half-integer position may cancel to 0.0 where the fp32 reference keeps a tiny
+    residue; the padding pattern is then pinned by the oracle applied to the values the block actually stores."""
+    import oracle
+    if isinstance(block._holder["pyr"], ops.Pyramid16):
+        stored = [v.cpu().numpy() for v in block.corr_pyramid]
+        c = coords.detach().cpu().numpy() if torch.is_tensor(coords) else np.asarray(coords)
+        return oracle.lookup(stored, c, radius) == 0
+    return np.asarray(ref) == 0

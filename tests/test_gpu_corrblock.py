@@ -8,7 +8,7 @@ import torch
 
 import oracle
 from oracle import torch_restatement as tr
-from helpers import rel_max
+from helpers import expected_zero_mask, rel_max
 
 warnings.filterwarnings("ignore")
 pytestmark = pytest.mark.gpu
@@ -31,7 +31,7 @@ def test_corrblock_forward_golden(golden, kind, precision, tol):
     ref = g[f"out_{kind}"]
     assert out.shape == ref.shape and out.is_contiguous() and out.dtype == torch.float32
     o = out.cpu().numpy()
-    assert np.array_equal(o == 0, ref == 0)        # indexing / zero-padding masks: exact
+    assert np.array_equal(o == 0, expected_zero_mask(blk, g[f"coords_{kind}"], 4, ref))   # zero-padding masks: exact
     assert rel_max(o, ref) <= tol
 
 
