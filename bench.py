@@ -6,7 +6,8 @@
 
 One "step" = one RAFT inference (12 refinement iterations) over a batch of 8 synthetic frame
 pairs per GPU: stock PyTorch/cuDNN encoders + update block (harness/raft_stock.py, random-init
-weights) around THIS repo's correlation path (pytorch-raft_b200/corr.py -> libraftcorr_b200.so).
+weights) around THIS repo's correlation path (pytorch-raft_b200/corr.py -> libraftcorr_b200.so),
+plus the library's convex-upsampling kernel (--stock-upsample switches it off).
 Frame pairs shard by batch across GPUs: no collective on the data path ("scaling": "weak").
 
   value      whole-job frame-pairs/s with the frames already resident in HBM (CUDA events,
@@ -15,12 +16,17 @@ Frame pairs shard by batch across GPUs: no collective on the data path ("scaling
              both frames and device -> host read of the full-resolution flow inside the timed
              region, every step
   roofline   the lookup kernel (the path's dominant kernel, 12 launches per step): algorithmic
-             bytes (2904 B/query) / its CUDA-event duration measured live inside
-             the timed region, against the measured HBM peak in MEASURED_PEAKS.json
+             bytes (2104 B/query on the 16-bit pyramid, 2904 B/query on the fp32
+             one) / its CUDA-event duration measured live inside the timed region, against the
+             measured HBM peak in MEASURED_PEAKS.json
+  roofline_build   the volume build against both of its roofs (tensor pipe, HBM write)
+  dropin_unchanged the UNMODIFIED reference raft.py (baseline/_ref) with this library's corr.py, and
+             with the reference's own corr.py, on the same GPU and frames
   cpu_baseline / --impl reference
-             the reference's CPU implementation of the path (oracle/torch_restatement.py issues
-             the same ATen ops as core/corr.py; /root/reference itself cannot travel) inside the
-             same harness model on the box's host cores, on a bounded sample (1 pair per step)
+             the reference's own CPU implementation (unmodified core/raft.py + core/corr.py from
+             baseline/_ref, kind "reference"; the oracle's torch restatement in the harness model
+             only when that copy is absent, kind "port") on the box's host cores, on a bounded
+             sample (1 pair per step)
 """
 from __future__ import annotations
 
@@ -222,6 +228,48 @@ def run_cpu_reference(steps: int, warmup: int, sample_pairs: int = 1):
                       + what}
 
 
+def measure_dropin_unchanged(dev, frames, steps: int = 5):
+    """What a user of the reference gets by putting pytorch-raft_b200/ ahead of core/ on sys.path and changing nothing
+    else: the UNMODIFIED reference raft.py (baseline/_ref, tools/install_ref.py) with this library's CorrBlock, same
+    frames, 12 iterations, test_mode.  The same model with the reference's own corr.py is timed beside it (stock
+    PyTorch on the same GPU).  Falls back to the harness model without its hooks when baseline/_ref is absent."""
+    from harness import ref_model
+
+    def timed(fn, reps, warm=2):
+        for _ in range(warm):
+            fn()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    B = frames[0].shape[0]
+    out = {}
+    if ref_model.available():
+        for key, dropin in (("with_this_library", True), ("reference_corr_py_on_this_gpu", False)):
+            raft = ref_model.load_raft_module(dropin=dropin)
+            torch.manual_seed(1234)
+            net = raft.RAFT(ref_model.make_args()).eval().to(dev)
+            with torch.no_grad():
+                ms = timed(lambda: net(frames[0], frames[1], iters=ITERS, test_mode=True), steps if dropin else 3)
+            out[key] = {"ms_per_step": ms, "frame_pairs_per_s": B / (ms * 1e-3)}
+            del net
+        out["model"] = "unmodified reference core/raft.py (baseline/_ref)"
+    else:
+        import corr as raftcorr_dropin
+        model = make_model(dev)
+        factory = lambda a, b, r: raftcorr_dropin.CorrBlock(a, b, num_levels=LEVELS, radius=r)  # noqa: E731
+        with torch.no_grad():
+            ms = timed(lambda: model(frames[0], frames[1], factory, iters=ITERS), steps)
+        out["with_this_library"] = {"ms_per_step": ms, "frame_pairs_per_s": B / (ms * 1e-3)}
+        out["model"] = "harness/raft_stock.py without hooks (baseline/_ref not installed)"
+    out["workload"] = "configs[1]: 440x1024, 12 iterations, batch 8, drop-in only (update.py and raft.py unchanged)"
+    return out
+
+
 def measure_other_configs(dev, hbm_peak_gbs, model=None, frames=None):
     """Kernel-level numbers for the path's other BASELINE.json configurations (CUDA events, rank 0,
     N=1 only; a few hundred ms): configs[3] on-the-fly path at 1088x1920, configs[4] training-step
@@ -258,9 +306,11 @@ def measure_other_configs(dev, hbm_peak_gbs, model=None, frames=None):
     T = sum((H >> l) * (W >> l) for l in range(4))
     compulsory = B * (N * D * 4 + T * D * 4 + 8 * N + 1296 * N)          # 120.4 MB per pair
     useful_flops = B * N * 4 * 100 * 2 * D
+    physical = B * (N * D * 2 + T * D * 2 + 8 * N + 1296 * N)            # the kernel reads bf16 copies of the fmaps
     out["alt_cfg4"] = {"workload": "AlternateCorrBlock 1088x1920 (136x240 fmaps), batch 4, D=256, smooth flow",
                        "ms_per_iter": ms, "compulsory_gb_s": compulsory / ms / 1e6,
                        "frac_hbm_at_compulsory_bytes": compulsory / ms / 1e6 / hbm_peak_gbs,
+                       "frac_hbm_at_physical_bf16_bytes": physical / ms / 1e6 / hbm_peak_gbs,
                        "useful_tflops": useful_flops / ms / 1e9, "binding": "sampler issue slots (tensor pipe 27 % active)"}
     del f1, f2, blk
     # configs[4]: CorrBlock forward + backward of 12 lookups at 368x496, batch 12
@@ -358,9 +408,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=None, help="bf16 (default) | tf32 | fp32 for the volume build")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
-    ap.add_argument("--stock-convc1", action="store_true",
-                    help="run convc1 + bias + ReLU (update.py:83,90) as stock torch ops on an NCHW lookup instead of "
-                         "the library's tensor-core 1x1 convolution on a channels-last lookup")
+    ap.add_argument("--tc-convc1", action="store_true",
+                    help="run convc1 + bias + ReLU (update.py:83,90) as the library's tensor-core 1x1 convolution on a "
+                         "channels-last lookup (needs the fp32 pyramid and an edited update.py) instead of stock torch ops")
+    ap.add_argument("--pyramid", default="auto", choices=["auto", "fp32", "bf16"],
+                    help="pyramid storage: auto = blocked bf16 whenever the build arithmetic is bf16")
     ap.add_argument("--stock-upsample", action="store_true",
                     help="run RAFT.upsample_flow as the reference's torch op sequence instead of this library's kernel")
     ap.add_argument("--cudnn-benchmark", action="store_true", help="let cuDNN autotune the stock convolutions")
@@ -412,9 +464,14 @@ def main():
         model = model.to(memory_format=torch.channels_last)
         dev1, dev2 = dev1.contiguous(memory_format=torch.channels_last), dev2.contiguous(memory_format=torch.channels_last)
     host_flow = torch.empty(BATCH_PER_GPU, 2, IMG_H, IMG_W).pin_memory()
+    args.stock_convc1 = not args.tc_convc1
+    nhwc_lookup = args.channels_last or args.tc_convc1
+    storage = "fp32" if nhwc_lookup else args.pyramid          # the channels-last lookup reads the fp32 pyramid
+    from raftcorr_b200 import ops
+    storage16 = ops.resolve_storage(storage, ops.resolve_precision(args.precision), 256, LEVELS, RADIUS) == "bf16"
     factory = lambda f1, f2, r: raftcorr_dropin.CorrBlock(f1, f2, num_levels=LEVELS, radius=r,  # noqa: E731
-                                                          precision=args.precision,
-                                                          channels_last=args.channels_last or not args.stock_convc1)
+                                                          precision=args.precision, channels_last=nhwc_lookup,
+                                                          storage=storage)
     convc1_fn = None if args.stock_convc1 else raftcorr_dropin.conv1x1_relu
 
     lookup_events = []
@@ -487,12 +544,14 @@ def main():
         step_resident()
     step_e2e()
 
-    def timed(fn, steps):
+    def timed(fn, steps, drain=None):
         barrier()
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0.record()
         for _ in range(steps):
             fn()
+        if drain is not None:
+            drain()              # work queued on other streams completes inside the timed region
         t1.record()
         barrier()
         ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
@@ -515,21 +574,23 @@ def main():
     if rank == 0:
         sampler.t1 = time.perf_counter()
     clocks = sampler.stop() if rank == 0 else None
-    ms_e2e = timed(step_e2e, args.steps)
+    # the last step's device -> host copy runs on copy_stream: make the timing stream wait for it before t1
+    ms_e2e = timed(step_e2e, args.steps, drain=lambda: torch.cuda.current_stream().wait_stream(copy_stream))
 
-    # kernel shares: the build (pack x2 + tcgen05 GEMM) once per step, timed on its own
-    fm = torch.randn(BATCH_PER_GPU, 256, IMG_H // 8, IMG_W // 8, device=dev)
-    fm2 = torch.randn_like(fm)
-    from raftcorr_b200 import ops
-    for _ in range(2):
-        ops.build_pyramid(fm, fm2, LEVELS, args.precision)
+    # kernel shares: the build (pack + tcgen05 GEMM with the pooled epilogue) once per step, timed on its own with the
+    # operands rotated so that no launch finds its inputs or outputs in L2
+    fms = [(torch.randn(BATCH_PER_GPU, 256, IMG_H // 8, IMG_W // 8, device=dev),
+            torch.randn(BATCH_PER_GPU, 256, IMG_H // 8, IMG_W // 8, device=dev)) for _ in range(2)]
+    for i in range(2):
+        ops.build_pyramid(*fms[i], LEVELS, args.precision, storage=storage, radius=RADIUS)
     b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     b0.record()
-    for _ in range(5):
-        ops.build_pyramid(fm, fm2, LEVELS, args.precision)
+    for i in range(6):
+        ops.build_pyramid(*fms[i & 1], LEVELS, args.precision, storage=storage, radius=RADIUS)
     b1.record()
     torch.cuda.synchronize()
-    build_ms = b0.elapsed_time(b1) / 5
+    build_ms = b0.elapsed_time(b1) / 6
+    del fms
 
     if rank != 0:
         if distributed:
@@ -542,7 +603,34 @@ def main():
     lookup_avg_ms = sum(lookup_ms) / max(len(lookup_ms), 1)
     queries = BATCH_PER_GPU * (IMG_H // 8) * (IMG_W // 8)
     peak, peak_src = measured_peaks()
-    achieved = queries * LOOKUP_BYTES_PER_QUERY / (lookup_avg_ms * 1e-3) / 1e9
+    bytes_per_query = lookup_bytes_per_query(2 if storage16 else 4)
+    achieved = queries * bytes_per_query / (lookup_avg_ms * 1e-3) / 1e9
+    if storage16:
+        lookup_kernel, traffic_key = "lookup16_kernel (bf16 pyramid in 64-byte blocks, NCHW output)", "lookup16_kernel"
+    elif nhwc_lookup:
+        lookup_kernel, traffic_key = "lookup_fwd_tma_kernel (fp32 pyramid, channels-last output)", "lookup_fwd_tma_kernel_nhwc"
+    else:
+        lookup_kernel, traffic_key = "lookup_fwd_tma_kernel (fp32 pyramid, NCHW output)", "lookup_fwd_tma_kernel"
+    # the build against both of its roofs: 2 N^2 D flops per pair on the tensor pipe, the pyramid
+    # written once to HBM; whichever is closer to its peak binds
+    peaks_all = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    Nq = (IMG_H // 8) * (IMG_W // 8)
+    T = sum(((IMG_H // 8) >> l) * ((IMG_W // 8) >> l) for l in range(LEVELS))
+    build_flops = 2.0 * BATCH_PER_GPU * Nq * Nq * 256
+    build_bytes = BATCH_PER_GPU * Nq * (T * (2 if storage16 else 4) + 2 * 256 * 4)
+    tf_sust = float(peaks_all.get("bf16_tflops_sustained", 1400.0))
+    tf_burst = float(peaks_all.get("bf16_tflops", 1590.0))
+    build_tflops = build_flops / (build_ms * 1e-3) / 1e12
+    build_gbs = build_bytes / (build_ms * 1e-3) / 1e9
+    roofline_build = {
+        "kernel": "pack2_bf16_kernel + build_tc_kernel (tcgen05 M128 N256, " + ("bf16 blocked" if storage16 else "fp32") + " pyramid epilogue)",
+        "ms": build_ms, "flops": build_flops, "algorithmic_bytes": build_bytes,
+        "tensor": {"achieved_tflops": build_tflops, "peak_sustained": tf_sust, "frac_sustained": build_tflops / tf_sust,
+                   "peak_burst": tf_burst, "frac_burst": build_tflops / tf_burst,
+                   "which": "bf16 dense, cuBLAS 8192^3 (MEASURED_PEAKS.json)" if peaks_all else "fallback"},
+        "hbm": {"achieved_gbs": build_gbs, "peak": peak, "frac": build_gbs / peak},
+        "bound": "tensor" if build_tflops / tf_sust >= build_gbs / peak else "hbm-write",
+    }
     h2d = 2 * BATCH_PER_GPU * 3 * IMG_H * IMG_W * 4
     d2h = BATCH_PER_GPU * 2 * IMG_H * IMG_W * 4
 
@@ -554,7 +642,8 @@ def main():
         "data": "synthetic",
         "config": dict(base_config, l2="inputs exceed L2 (2.1 GB pyramid + 115 MB frames per step)",
                        build_precision=args.precision or "bf16", encoders="stock PyTorch/cuDNN fp32",
-                       convc1="stock torch conv2d + relu on an NCHW lookup" if args.stock_convc1 else
+                       pyramid="bf16 in 4x8-pixel 64-byte blocks (raftcorr_level16)" if storage16 else "fp32 rows (raftcorr_level)",
+                       convc1="stock torch conv2d + relu on an NCHW lookup (update.py unchanged)" if args.stock_convc1 else
                        "raftcorr_conv1x1_nhwc_fwd (tf32 tcgen05, bias + ReLU epilogue) on a channels-last lookup",
                        upsample="stock torch ops (raft.py:72-83)" if args.stock_upsample else
                        "raftcorr_upsample_flow_fwd, every iteration like the reference",
@@ -564,18 +653,23 @@ def main():
                 "copies": "pinned host <-> device on a second stream, double-buffered, overlapping the neighbouring steps"},
         # pack + tcgen05 build + 12 lookups (+ 12 tensor-core 1x1 convolutions, + 12 convex upsamplings) per step
         "gpu_launches": (2 + ITERS * (1 + (not args.stock_upsample) + (not args.stock_convc1))) * args.steps * n_gpus,
-        "roofline": {"kernel": "lookup_fwd_tma_kernel" + ("" if args.stock_convc1 and not args.channels_last
-                                                          else " (channels-last output)"),
+        "roofline": {"kernel": lookup_kernel,
                      "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic_per_launch(args.channels_last or not args.stock_convc1),
-                     "peak_source": peak_src, "algorithmic_bytes_per_launch": queries * LOOKUP_BYTES_PER_QUERY,
-                     "launch_us": lookup_avg_ms * 1e3, "launches_timed": len(lookup_ms)},
+                     "traffic": ncu_traffic_per_launch(traffic_key),
+                     "peak_source": peak_src, "algorithmic_bytes_per_query": bytes_per_query,
+                     "algorithmic_bytes_per_launch": queries * bytes_per_query,
+                     "launch_us": lookup_avg_ms * 1e3, "launches_timed": len(lookup_ms),
+                     "note": "launch_us averages all 12 launches of a step, including iteration 0 whose integer "
+                             "coordinates take the kernel's slower floor-flip path"},
+        "roofline_build": roofline_build,
         "kernels": {"lookup_us": lookup_avg_ms * 1e3, "build_ms": build_ms,
                     "corr_path_ms_per_step": build_ms + ITERS * lookup_avg_ms,
                     "corr_path_share_of_step": (build_ms + ITERS * lookup_avg_ms) / (ms_total / args.steps)},
         "clocks": clocks,
     }
     if n_gpus == 1:
+        line["dropin_unchanged"] = measure_dropin_unchanged(dev, (dev1, dev2))
+        line["measured_here"] = measure_tf32_peak(dev)
         line["other_configs"] = measure_other_configs(dev, peak, model, (dev1, dev2))
     if not args.skip_cpu_baseline and n_gpus == 1:
         ref = run_cpu_reference(steps=1, warmup=1)
