@@ -659,6 +659,8 @@ def main():
                      "peak_source": peak_src, "algorithmic_bytes_per_query": bytes_per_query,
                      "algorithmic_bytes_per_launch": queries * bytes_per_query,
                      "launch_us": lookup_avg_ms * 1e3, "launches_timed": len(lookup_ms),
+                     "launch_us_by_iteration": [round(1e3 * sum(lookup_ms[i::ITERS]) / max(len(lookup_ms[i::ITERS]), 1), 2)
+                                                for i in range(ITERS)],
                      "note": "launch_us averages all 12 launches of a step, including iteration 0 whose integer "
                              "coordinates take the kernel's slower floor-flip path"},
         "roofline_build": roofline_build,
