@@ -126,10 +126,9 @@ __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img
 //                   of x tap i is carried over as the left-hand column of tap i+1)
 //   kChain = false: floor flips of the coordinate round trip somewhere in the warp (integer coordinates: RAFT's
 //                   first iteration): four loads per sample at the taps' own positions
-template <int R, bool kChain, int kIB, int kIE, bool kAllLive, typename Between>
+template <int R, bool kChain, int kIB, int kIE, bool kAllLive>
 __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0, int by0, const Tap (&tx)[2 * R + 1],
-                                            const Tap (&ty)[2 * R + 1], float* optr, long long N, bool live,
-                                            Between&& between) {
+                                            const Tap (&ty)[2 * R + 1], float* optr, long long N, bool live) {
   constexpr int rd = 2 * R + 1;   // this warp forms the samples of x taps kIB .. kIE-1
   const int rowpitch = bw * 64;   // bytes per block row of the box
   auto row_off = [&](int yy) { return slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16); };
@@ -152,34 +151,30 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
   }
   float* o = optr + (long long)(kIB * rd) * N;
   if constexpr (kChain) {
-    // Phase 1: the whole (rd+1) x (kIE-kIB+1) patch this warp needs goes into registers; then between() hands the
-    // buffer back (the pair refills it with its next unit) and phase 2 — arithmetic and stores, most of the time —
-    // runs while those boxes are in flight.
-    constexpr int kCols = kIE - kIB + 1;
-    float pxl[kCols][rd + 1];
+    uint32_t rows[rd + 1];
+    const int yy0 = ty[0].i0 - 4 * by0, xx0 = tx[0].i0 - 8 * bx0;
+#pragma unroll
+    for (int r = 0; r <= rd; ++r) rows[r] = row_off(yy0 + r);
+    float left[rd + 1], right[rd + 1];
     {
-      uint32_t rows[rd + 1];
-      const int yy0 = ty[0].i0 - 4 * by0, xx0 = tx[0].i0 - 8 * bx0;
+      const uint32_t c = col_off(xx0 + kIB);
 #pragma unroll
-      for (int r = 0; r <= rd; ++r) rows[r] = row_off(yy0 + r);
-#pragma unroll
-      for (int c = 0; c < kCols; ++c) {
-        const uint32_t co = col_off(xx0 + kIB + c);
-#pragma unroll
-        for (int r = 0; r <= rd; ++r) pxl[c][r] = px(rows[r], co);
-      }
+      for (int r = 0; r <= rd; ++r) left[r] = px(rows[r], c);
     }
-    between();
 #pragma unroll
     for (int i = kIB; i < kIE; ++i) {
+      const uint32_t c = col_off(xx0 + i + 1);
       const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
 #pragma unroll
+      for (int r = 0; r <= rd; ++r) right[r] = px(rows[r], c);
+#pragma unroll
       for (int j = 0; j < rd; ++j) {
-        const float v = combine(pxl[i - kIB][j], pxl[i - kIB + 1][j], pxl[i - kIB][j + 1], pxl[i - kIB + 1][j + 1], fx, ex,
-                                fy[j], sy[j]);
+        const float v = combine(left[j], right[j], left[j + 1], right[j + 1], fx, ex, fy[j], sy[j]);
         if (kAllLive || live) __stcs(o, v);
         o += N;
       }
+#pragma unroll
+      for (int r = 0; r <= rd; ++r) left[r] = right[r];
     }
   } else {
     uint32_t rtop[rd], rbot[rd];
@@ -201,7 +196,85 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
         o += N;
       }
     }
-    between();
+  }
+}
+
+// The same samples when floor flips break the tap chains (RAFT's first iteration starts on the integer grid, where
+// the reference's coordinate round trip moves floor() down by one on ~8 % of the taps): tap j then sits on pixel
+// m + j + e_j with e_j in {0, 1} (m = min_j(i0_j - j)), so the footprint is still a dense patch — rd+2 rows, one more
+// column — and the patch is loaded once, column by column as in the chain case; which of two neighbouring rows /
+// columns a tap uses is a per-lane select on registers instead of a per-lane address.
+template <int R, int kIB, int kIE, bool kAllLive>
+__device__ __forceinline__ void sample_unit_flips(uint32_t slot_addr, int bw, int bh, int bx0, int by0, int mx, int my,
+                                                  const Tap (&tx)[2 * R + 1], const Tap (&ty)[2 * R + 1], float* optr,
+                                                  long long N, bool live) {
+  constexpr int rd = 2 * R + 1, kRows = rd + 2;
+  const int rowpitch = bw * 64;
+  auto px = [&](uint32_t row, uint32_t col) -> float {
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz64(row + col)));
+    return bf16_bits_to_float(v);
+  };
+  auto combine = [&](float vnw, float vne, float vsw, float vse, float w_, float e_, float n_, float s_) {
+    const float nw = __fmul_rn(s_, e_), ne = __fmul_rn(s_, w_), sw = __fmul_rn(n_, e_), se = __fmul_rn(n_, w_);
+    return __fmaf_rn(vse, se, __fmaf_rn(vsw, sw, __fmaf_rn(vne, ne, __fmul_rn(vnw, nw))));
+  };
+  // rows / columns of the patch that no tap of this lane uses may fall outside the box: clamp their addresses into
+  // the slot (the values are loaded but never selected)
+  uint32_t rows[kRows];
+#pragma unroll
+  for (int r = 0; r < kRows; ++r) {
+    const int yy = max(0, min(my + r - 4 * by0, 4 * bh - 1));
+    rows[r] = slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16);
+  }
+  auto col_off = [&](int c) {
+    const int xx = max(0, min(mx + c - 8 * bx0, 8 * bw - 1));
+    return (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
+  };
+  float fy[rd], sy[rd];
+  bool ey[rd];
+#pragma unroll
+  for (int j = 0; j < rd; ++j) {
+    fy[j] = ty[j].frac;
+    sy[j] = __fsub_rn(1.0f, fy[j]);
+    ey[j] = (ty[j].i0 - j) != my;
+  }
+  float c0[kRows], c1[kRows], c2[kRows];
+  {
+    const uint32_t a = col_off(kIB), b = col_off(kIB + 1);
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      c0[r] = px(rows[r], a);
+      c1[r] = px(rows[r], b);
+    }
+  }
+  float* o = optr + (long long)(kIB * rd) * N;
+#pragma unroll
+  for (int i = kIB; i < kIE; ++i) {
+    const uint32_t c = col_off(i + 2);
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) c2[r] = px(rows[r], c);
+    const bool ex_ = (tx[i].i0 - i) != mx;
+    const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
+    float lft[kRows], rgt[kRows];
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      lft[r] = ex_ ? c1[r] : c0[r];
+      rgt[r] = ex_ ? c2[r] : c1[r];
+    }
+#pragma unroll
+    for (int j = 0; j < rd; ++j) {
+      const float tl = ey[j] ? lft[j + 1] : lft[j], bl = ey[j] ? lft[j + 2] : lft[j + 1];
+      const float tr = ey[j] ? rgt[j + 1] : rgt[j], br = ey[j] ? rgt[j + 2] : rgt[j + 1];
+      const float v = combine(tl, tr, bl, br, fx, ex, fy[j], sy[j]);
+      if (kAllLive || live) __stcs(o, v);
+      o += N;
+    }
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      c0[r] = c1[r];
+      c1[r] = c2[r];
+    }
   }
 }
 
@@ -325,34 +398,43 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
       if (j) chain &= (ty[j].i0 == ty[j - 1].i0 + 1) & (tx[j].i0 == tx[j - 1].i0 + 1);
     }
     const Window w = window_from(tx[0].i0, tx[rd - 1].i0 + 1, ty[0].i0, ty[rd - 1].i0 + 1);   // = what issue() used
-    const int bw = 2 + w.wide;
+    const int bw = 2 + w.wide, bh = 3 + w.tall;
+    // floor flips: is tap j on pixel m + j + e_j with e_j in {0,1}?
+    int mx = tx[0].i0, my = ty[0].i0, hx = tx[0].i0, hy = ty[0].i0;
+#pragma unroll
+    for (int j = 1; j < rd; ++j) {
+      mx = min(mx, tx[j].i0 - j);
+      hx = max(hx, tx[j].i0 - j);
+      my = min(my, ty[j].i0 - j);
+      hy = max(hy, ty[j].i0 - j);
+    }
+    const bool flips_ok = (hx - mx <= 1) & (hy - my <= 1);
     const bool live = cur.live;
     const bool all_fast = __all_sync(0xffffffffu, w.fast || !live);
     const bool all_chain = __all_sync(0xffffffffu, chain || !live);
     const bool all_live = __all_sync(0xffffffffu, live);
     mbar_wait(bar, phase, 2);
     phase ^= 1u;
-    // hand the buffer back: both warps of the pair are done reading it before either refills it
-    auto refill = [&]() {
-      if (more) {
-        asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
-        issue(nxt);
-      }
-    };
     if (p.debug & 1) {
-      refill();
     } else if (!all_fast) {
       if (live) sample_unit_global<R, kMode>(lv, cur.img, cur.cxl, cur.cyl, h ? kMid : 0, h ? rd : kMid, cur.optr, N);
-      refill();
     } else if (all_chain && all_live) {
-      if (h == 0) sample_unit<R, true, 0, kMid, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
-      else sample_unit<R, true, kMid, rd, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
+      if (h == 0) sample_unit<R, true, 0, kMid, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      else sample_unit<R, true, kMid, rd, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
     } else if (all_chain) {
-      if (h == 0) sample_unit<R, true, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
-      else sample_unit<R, true, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
+      if (h == 0) sample_unit<R, true, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      else sample_unit<R, true, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+    } else if (__all_sync(0xffffffffu, flips_ok || !live)) {
+      if (h == 0) sample_unit_flips<R, 0, kMid, false>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, tx, ty, cur.optr, N, live);
+      else sample_unit_flips<R, kMid, rd, false>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, tx, ty, cur.optr, N, live);
     } else {
-      if (h == 0) sample_unit<R, false, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
-      else sample_unit<R, false, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live, refill);
+      if (h == 0) sample_unit<R, false, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      else sample_unit<R, false, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+    }
+    if (more) {
+      // both warps of the pair are done reading the buffer before either refills it
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
+      issue(nxt);
     }
     cur = nxt;
   }
