@@ -120,19 +120,24 @@ __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img
   return bf16_bits_to_float(*reinterpret_cast<const unsigned short*>(p));
 }
 
-// One query's (2r+1)^2 samples at one level, from its slot.  Two code shapes:
-//   kChain = true : x and y taps sit on consecutive pixels for every lane of the warp (the usual case): the
-//                   window is a dense (rd+1) x (rd+1) patch and every pixel is loaded once (the right-hand column
-//                   of x tap i is carried over as the left-hand column of tap i+1)
-//   kChain = false: floor flips of the coordinate round trip somewhere in the warp (integer coordinates: RAFT's
-//                   first iteration): four loads per sample at the taps' own positions
-template <int R, bool kChain, int kIB, int kIE, bool kAllLive>
-__device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0, int by0, const Tap (&tx)[2 * R + 1],
-                                            const Tap (&ty)[2 * R + 1], float* optr, long long N, bool live) {
-  constexpr int rd = 2 * R + 1;   // this warp forms the samples of x taps kIB .. kIE-1
+// One query's samples at one level for x taps [i_begin, i_end), out of its slot.
+//
+// Tap j of an axis sits on pixel m + j + e_j with m = min_j(i0_j - j).  Normally every e_j is 0 (kFlips = false):
+// the footprint is a dense (rd+1) x (rd+1) patch, each pixel is loaded once, and the right-hand column of x tap i is
+// carried over as the left-hand column of tap i+1.  On the integer grid (RAFT's first iteration) the reference's
+// coordinate round trip moves floor() down by one on ~8 % of the taps: e_j is then 0 or 1 per lane and tap
+// (kFlips = true), the patch grows by one row and one column, it is still loaded once, and which of two
+// neighbouring rows / columns a tap uses is a per-lane select on registers.
+//
+// The x-tap loop is a real loop (the taps are recomputed from the loop counter, ~14 instructions): fully unrolled,
+// the variants of this routine came to 10k SASS instructions and the warps of an SM — each in a different variant
+// or phase — spent 40 % of their issue slots waiting for the instruction cache.
+template <int R, int kMode, bool kFlips, bool kAllLive>
+__device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bh, int bx0, int by0, int mx, int my,
+                                            float cxl, const Level16Dev& lv, const Tap (&ty)[2 * R + 1], int i_begin,
+                                            int i_end, float* optr, long long N, bool live) {
+  constexpr int rd = 2 * R + 1, kRows = rd + 1 + (kFlips ? 1 : 0);
   const int rowpitch = bw * 64;   // bytes per block row of the box
-  auto row_off = [&](int yy) { return slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16); };
-  auto col_off = [&](int xx) { return (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2); };
   auto px = [&](uint32_t row, uint32_t col) -> float {
     unsigned short v;
     asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz64(row + col)));
@@ -143,92 +148,18 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bx0,
     const float nw = __fmul_rn(s_, e_), ne = __fmul_rn(s_, w_), sw = __fmul_rn(n_, e_), se = __fmul_rn(n_, w_);
     return __fmaf_rn(vse, se, __fmaf_rn(vsw, sw, __fmaf_rn(vne, ne, __fmul_rn(vnw, nw))));
   };
-  float fy[rd], sy[rd];
-#pragma unroll
-  for (int j = 0; j < rd; ++j) {
-    fy[j] = ty[j].frac;
-    sy[j] = __fsub_rn(1.0f, fy[j]);
-  }
-  float* o = optr + (long long)(kIB * rd) * N;
-  if constexpr (kChain) {
-    uint32_t rows[rd + 1];
-    const int yy0 = ty[0].i0 - 4 * by0, xx0 = tx[0].i0 - 8 * bx0;
-#pragma unroll
-    for (int r = 0; r <= rd; ++r) rows[r] = row_off(yy0 + r);
-    float left[rd + 1], right[rd + 1];
-    {
-      const uint32_t c = col_off(xx0 + kIB);
-#pragma unroll
-      for (int r = 0; r <= rd; ++r) left[r] = px(rows[r], c);
-    }
-#pragma unroll
-    for (int i = kIB; i < kIE; ++i) {
-      const uint32_t c = col_off(xx0 + i + 1);
-      const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
-#pragma unroll
-      for (int r = 0; r <= rd; ++r) right[r] = px(rows[r], c);
-#pragma unroll
-      for (int j = 0; j < rd; ++j) {
-        const float v = combine(left[j], right[j], left[j + 1], right[j + 1], fx, ex, fy[j], sy[j]);
-        if (kAllLive || live) __stcs(o, v);
-        o += N;
-      }
-#pragma unroll
-      for (int r = 0; r <= rd; ++r) left[r] = right[r];
-    }
-  } else {
-    uint32_t rtop[rd], rbot[rd];
-#pragma unroll
-    for (int j = 0; j < rd; ++j) {
-      const int yy = ty[j].i0 - 4 * by0;
-      rtop[j] = row_off(yy);
-      rbot[j] = row_off(yy + 1);
-    }
-#pragma unroll
-    for (int i = kIB; i < kIE; ++i) {
-      const int xx = tx[i].i0 - 8 * bx0;
-      const uint32_t cl = col_off(xx), cr = col_off(xx + 1);
-      const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
-#pragma unroll
-      for (int j = 0; j < rd; ++j) {
-        const float v = combine(px(rtop[j], cl), px(rtop[j], cr), px(rbot[j], cl), px(rbot[j], cr), fx, ex, fy[j], sy[j]);
-        if (kAllLive || live) __stcs(o, v);
-        o += N;
-      }
-    }
-  }
-}
-
-// The same samples when floor flips break the tap chains (RAFT's first iteration starts on the integer grid, where
-// the reference's coordinate round trip moves floor() down by one on ~8 % of the taps): tap j then sits on pixel
-// m + j + e_j with e_j in {0, 1} (m = min_j(i0_j - j)), so the footprint is still a dense patch — rd+2 rows, one more
-// column — and the patch is loaded once, column by column as in the chain case; which of two neighbouring rows /
-// columns a tap uses is a per-lane select on registers instead of a per-lane address.
-template <int R, int kIB, int kIE, bool kAllLive>
-__device__ __forceinline__ void sample_unit_flips(uint32_t slot_addr, int bw, int bh, int bx0, int by0, int mx, int my,
-                                                  const Tap (&tx)[2 * R + 1], const Tap (&ty)[2 * R + 1], float* optr,
-                                                  long long N, bool live) {
-  constexpr int rd = 2 * R + 1, kRows = rd + 2;
-  const int rowpitch = bw * 64;
-  auto px = [&](uint32_t row, uint32_t col) -> float {
-    unsigned short v;
-    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz64(row + col)));
-    return bf16_bits_to_float(v);
-  };
-  auto combine = [&](float vnw, float vne, float vsw, float vse, float w_, float e_, float n_, float s_) {
-    const float nw = __fmul_rn(s_, e_), ne = __fmul_rn(s_, w_), sw = __fmul_rn(n_, e_), se = __fmul_rn(n_, w_);
-    return __fmaf_rn(vse, se, __fmaf_rn(vsw, sw, __fmaf_rn(vne, ne, __fmul_rn(vnw, nw))));
-  };
-  // rows / columns of the patch that no tap of this lane uses may fall outside the box: clamp their addresses into
-  // the slot (the values are loaded but never selected)
+  // Patch rows / columns that no tap of this lane uses may fall outside the box (flips only): their addresses are
+  // clamped into the slot; the values are loaded but never selected.
   uint32_t rows[kRows];
 #pragma unroll
   for (int r = 0; r < kRows; ++r) {
-    const int yy = max(0, min(my + r - 4 * by0, 4 * bh - 1));
+    int yy = my + r - 4 * by0;
+    if (kFlips) yy = max(0, min(yy, 4 * bh - 1));
     rows[r] = slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16);
   }
   auto col_off = [&](int c) {
-    const int xx = max(0, min(mx + c - 8 * bx0, 8 * bw - 1));
+    int xx = mx + c - 8 * bx0;
+    if (kFlips) xx = max(0, min(xx, 8 * bw - 1));
     return (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
   };
   float fy[rd], sy[rd];
@@ -237,35 +168,51 @@ __device__ __forceinline__ void sample_unit_flips(uint32_t slot_addr, int bw, in
   for (int j = 0; j < rd; ++j) {
     fy[j] = ty[j].frac;
     sy[j] = __fsub_rn(1.0f, fy[j]);
-    ey[j] = (ty[j].i0 - j) != my;
+    ey[j] = kFlips && (ty[j].i0 - j) != my;
   }
   float c0[kRows], c1[kRows], c2[kRows];
   {
-    const uint32_t a = col_off(kIB), b = col_off(kIB + 1);
+    const uint32_t a = col_off(i_begin), b = col_off(i_begin + 1);
 #pragma unroll
     for (int r = 0; r < kRows; ++r) {
       c0[r] = px(rows[r], a);
-      c1[r] = px(rows[r], b);
+      if (kFlips) c1[r] = px(rows[r], b);
     }
   }
-  float* o = optr + (long long)(kIB * rd) * N;
-#pragma unroll
-  for (int i = kIB; i < kIE; ++i) {
-    const uint32_t c = col_off(i + 2);
-#pragma unroll
-    for (int r = 0; r < kRows; ++r) c2[r] = px(rows[r], c);
-    const bool ex_ = (tx[i].i0 - i) != mx;
-    const float fx = tx[i].frac, ex = __fsub_rn(1.0f, fx);
+  float* o = optr + (long long)(i_begin * rd) * N;
+#pragma unroll 1
+  for (int i = i_begin; i < i_end; ++i) {
+    const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+    const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
     float lft[kRows], rgt[kRows];
+    if constexpr (kFlips) {
+      const uint32_t c = col_off(i + 2);
 #pragma unroll
-    for (int r = 0; r < kRows; ++r) {
-      lft[r] = ex_ ? c1[r] : c0[r];
-      rgt[r] = ex_ ? c2[r] : c1[r];
+      for (int r = 0; r < kRows; ++r) c2[r] = px(rows[r], c);
+      const bool flip = (t.i0 - i) != mx;
+#pragma unroll
+      for (int r = 0; r < kRows; ++r) {
+        lft[r] = flip ? c1[r] : c0[r];
+        rgt[r] = flip ? c2[r] : c1[r];
+      }
+    } else {
+      const uint32_t c = col_off(i + 1);
+#pragma unroll
+      for (int r = 0; r < kRows; ++r) {
+        c1[r] = px(rows[r], c);
+        lft[r] = c0[r];
+        rgt[r] = c1[r];
+      }
     }
 #pragma unroll
     for (int j = 0; j < rd; ++j) {
-      const float tl = ey[j] ? lft[j + 1] : lft[j], bl = ey[j] ? lft[j + 2] : lft[j + 1];
-      const float tr = ey[j] ? rgt[j + 1] : rgt[j], br = ey[j] ? rgt[j + 2] : rgt[j + 1];
+      float tl = lft[j], bl = lft[j + 1], tr = rgt[j], br = rgt[j + 1];
+      if constexpr (kFlips) {
+        tl = ey[j] ? lft[j + 1] : lft[j];
+        bl = ey[j] ? lft[j + 2] : lft[j + 1];
+        tr = ey[j] ? rgt[j + 1] : rgt[j];
+        br = ey[j] ? rgt[j + 2] : rgt[j + 1];
+      }
       const float v = combine(tl, tr, bl, br, fx, ex, fy[j], sy[j]);
       if (kAllLive || live) __stcs(o, v);
       o += N;
@@ -273,7 +220,7 @@ __device__ __forceinline__ void sample_unit_flips(uint32_t slot_addr, int bw, in
 #pragma unroll
     for (int r = 0; r < kRows; ++r) {
       c0[r] = c1[r];
-      c1[r] = c2[r];
+      if (kFlips) c1[r] = c2[r];
     }
   }
 }
@@ -415,21 +362,19 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     const bool all_live = __all_sync(0xffffffffu, live);
     mbar_wait(bar, phase, 2);
     phase ^= 1u;
+    const bool all_flips = __all_sync(0xffffffffu, flips_ok || !live);
+    const int ib = h ? kMid : 0, ie = h ? rd : kMid;
     if (p.debug & 1) {
-    } else if (!all_fast) {
-      if (live) sample_unit_global<R, kMode>(lv, cur.img, cur.cxl, cur.cyl, h ? kMid : 0, h ? rd : kMid, cur.optr, N);
+    } else if (!all_fast || !all_flips) {
+      // a window that does not fit a box (|coords| beyond ~2^20) or an irregular tap pattern somewhere in the warp:
+      // every lane samples straight from global memory
+      if (live) sample_unit_global<R, kMode>(lv, cur.img, cur.cxl, cur.cyl, ib, ie, cur.optr, N);
     } else if (all_chain && all_live) {
-      if (h == 0) sample_unit<R, true, 0, kMid, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
-      else sample_unit<R, true, kMid, rd, true>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      sample_unit<R, kMode, false, true>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
     } else if (all_chain) {
-      if (h == 0) sample_unit<R, true, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
-      else sample_unit<R, true, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
-    } else if (__all_sync(0xffffffffu, flips_ok || !live)) {
-      if (h == 0) sample_unit_flips<R, 0, kMid, false>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, tx, ty, cur.optr, N, live);
-      else sample_unit_flips<R, kMid, rd, false>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, tx, ty, cur.optr, N, live);
+      sample_unit<R, kMode, false, false>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
     } else {
-      if (h == 0) sample_unit<R, false, 0, kMid, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
-      else sample_unit<R, false, kMid, rd, false>(slot_addr, bw, w.bx0, w.by0, tx, ty, cur.optr, N, live);
+      sample_unit<R, kMode, true, false>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
     }
     if (more) {
       // both warps of the pair are done reading the buffer before either refills it
