@@ -180,7 +180,7 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bh, 
     }
   }
   float* o = optr + (long long)(i_begin * rd) * N;
-#pragma unroll 1
+#pragma unroll 2
   for (int i = i_begin; i < i_end; ++i) {
     const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
     const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
@@ -275,31 +275,58 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     float* optr;
     bool live;
   };
-  auto unit_at = [&](int k, float cx, float cy) {
+  // Tile cursors advance incrementally (a pair steps through tiles blockIdx + k * gridDim, k = first, first + 2, ...):
+  // decoding a tile index costs two integer divisions, ~50 instructions each time, for every lane.
+  struct Cursor {
+    int tx, y, b;
+  };
+  const int tiles_x = p.tiles_x, fmH = p.H;
+  auto cursor_at = [&](int k) {
+    Cursor c;
+    const unsigned tile = blockIdx.x + (unsigned)k * gridDim.x;
+    const unsigned t2 = tile / (unsigned)tiles_x;
+    c.tx = (int)(tile - t2 * (unsigned)tiles_x);
+    c.b = (int)(t2 / (unsigned)fmH);
+    c.y = (int)(t2 - (unsigned)c.b * (unsigned)fmH);
+    return c;
+  };
+  Cursor step;   // kDepth16 * gridDim tiles, decomposed the same way
+  {
+    const unsigned st = (unsigned)kDepth16 * gridDim.x, t2 = st / (unsigned)tiles_x;
+    step.tx = (int)(st - t2 * (unsigned)tiles_x);
+    step.b = (int)(t2 / (unsigned)fmH);
+    step.y = (int)(t2 - (unsigned)step.b * (unsigned)fmH);
+  }
+  auto advance = [&](Cursor& c) {
+    c.tx += step.tx;
+    if (c.tx >= tiles_x) {
+      c.tx -= tiles_x;
+      c.y += 1;
+    }
+    c.y += step.y;
+    if (c.y >= fmH) {
+      c.y -= fmH;
+      c.b += 1;
+    }
+    c.b += step.b;
+  };
+  auto unit_at = [&](const Cursor& c, float cx, float cy) {
     Unit u;
-    const unsigned tile = blockIdx.x + (unsigned)k * gridDim.x;       // 32-bit arithmetic only
-    const unsigned t2 = tile / (unsigned)p.tiles_x;
-    const int x = (int)(tile - t2 * (unsigned)p.tiles_x) * kTileQ + lane;
-    const int b = (int)(t2 / (unsigned)p.H);
-    const int y = (int)(t2 - (unsigned)b * (unsigned)p.H);
+    const int x = c.tx * kTileQ + lane;
     u.live = x < p.W;
-    u.img = (long long)b * N + (long long)y * p.W + x;
-    u.optr = p.out + ((long long)b * kChannels + level * rd2) * N + (long long)y * p.W + x;
+    u.img = (long long)c.b * N + (long long)c.y * p.W + x;
+    u.optr = p.out + ((long long)c.b * kChannels + level * rd2) * N + (long long)c.y * p.W + x;
     u.cxl = __fmul_rn(cx, lv.inv_pow2);
     u.cyl = __fmul_rn(cy, lv.inv_pow2);
     return u;
   };
-  auto load_coords = [&](int k, float& cx, float& cy) {
+  auto load_coords = [&](const Cursor& c, bool in_range, float& cx, float& cy) {
     cx = cy = 0.0f;
-    if (k >= n_tiles) return;
-    const unsigned tile = blockIdx.x + (unsigned)k * gridDim.x;
-    const unsigned t2 = tile / (unsigned)p.tiles_x;
-    const int x = (int)(tile - t2 * (unsigned)p.tiles_x) * kTileQ + lane;
-    if (x < p.W) {
-      const unsigned b = t2 / (unsigned)p.H;
-      const float* c = p.coords + (long long)(t2 + b * (unsigned)p.H) * p.W + x;   // (b*2*H + y) * W + x
-      cx = __ldg(c);
-      cy = __ldg(c + N);
+    const int x = c.tx * kTileQ + lane;
+    if (in_range && x < p.W) {
+      const float* ptr = p.coords + ((long long)c.b * 2 * fmH + c.y) * p.W + x;
+      cx = __ldg(ptr);
+      cy = __ldg(ptr + N);
     }
   };
   // this warp requests the boxes of lanes 16h .. 16h+15 of the pair's next unit
@@ -317,10 +344,13 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     }
   };
 
-  float ncx, ncy;
-  load_coords(first, ncx, ncy);
   if (first >= n_tiles) return;
-  Unit cur = unit_at(first, ncx, ncy);
+  float ncx, ncy;
+  Cursor cu = cursor_at(first);            // the unit about to be fetched / sampled
+  load_coords(cu, true, ncx, ncy);
+  Unit cur = unit_at(cu, ncx, ncy);
+  advance(cu);                             // -> first + 2
+  Cursor cc = cu;                          // the tile whose coordinates are loaded next
   // All pairs take the same time per unit, so pairs that start together stay in lock step: every pair waits for
   // its boxes at the same moment and every pair samples at the same moment.  Half of them start one microsecond
   // late (measured best; RAFTCORR_L16_DEBUG bits 8.. override it in units of 256 ns, 255 = none).
@@ -329,13 +359,16 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     for (unsigned t = 0; t < steps && steps != 255u; ++t) __nanosleep(256);
   }
   issue(cur);
-  load_coords(first + kDepth16, ncx, ncy);
+  load_coords(cc, first + kDepth16 < n_tiles, ncx, ncy);
+  advance(cc);                             // -> first + 4
   uint32_t phase = 0;
   for (int k = first; k < n_tiles; k += kDepth16) {
     const bool more = k + kDepth16 < n_tiles;
     Unit nxt = cur;
-    if (more) nxt = unit_at(k + kDepth16, ncx, ncy);
-    load_coords(k + 2 * kDepth16, ncx, ncy);           // two units ahead
+    if (more) nxt = unit_at(cu, ncx, ncy);
+    advance(cu);
+    load_coords(cc, k + 2 * kDepth16 < n_tiles, ncx, ncy);   // two units ahead
+    advance(cc);
     Tap tx[rd], ty[rd];
     bool chain = true;
 #pragma unroll
