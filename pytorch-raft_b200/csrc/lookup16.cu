@@ -8,16 +8,19 @@
 // Here a LANE owns a query:
 //
 //   unit      = 32 consecutive-x queries of one fmap row at ONE pyramid level (4 units per tile)
-//   warp pair = owns one unit buffer and walks every other tile of its level (8 pairs: 4 levels x 2).  Lane q
-//               derives its query's window; the pair requests one TMA box per lane (cp.async.bulk.tensor.4d over
+//   warp      = owns one unit buffer and walks every other tile of its level (8 warps: 4 levels x 2).  Lane q
+//               derives its query's window and the warp requests one TMA box per lane (cp.async.bulk.tensor.4d over
 //               the level's (64-byte block, blocks_x, blocks_y, image) tensor: {2,3} x {3,4} whole blocks;
-//               out-of-image blocks arrive as zeros = grid_sample's zero padding; each warp issues 16 of them,
-//               no producer warp: one warp can issue a box only every ~140 cycles) into the lane's slot, all 32
+//               out-of-image blocks arrive as zeros = grid_sample's zero padding) into the lane's slot, all 32
 //               boxes on one mbarrier.  When they have landed, lane q forms its query's (2r+1)^2 samples out of
-//               its own slot (the two warps split the x taps) and stores them straight to the NCHW output — for
-//               a fixed channel the 32 lanes are 32 consecutive x, so every store instruction is one full
-//               128-byte line and the output never passes through shared memory.  Then the pair refills its
-//               buffer with its next unit; the other seven pairs keep the SM busy meanwhile.
+//               its own slot and stores them straight to the NCHW output — for a fixed channel the 32 lanes are
+//               32 consecutive x, so every store instruction is one full 128-byte line and the output never
+//               passes through shared memory.  Then the warp refills its buffer with its next unit; the other
+//               seven warps keep the SM busy meanwhile.
+//               (Measured alternatives, all slower at BASELINE.json configs[1]: dedicated producer warps — one
+//               warp issues a box only every ~140 cycles; two warps per unit splitting the x taps — the per-unit
+//               work (tap tables, window, issue) is then paid twice; staging the patch in registers to refill
+//               early; L2 prefetch of the next unit.  RAFTCORR_L16_SPLIT=2 builds the two-warp variant.)
 //
 // Shared memory: 8 unit buffers x 32 slots x 896 B.  The 32 windows are walked in lock step, at the same
 // in-window offset more often than not, and TMA wants 128-byte aligned destinations, so unskewed slots would put
@@ -42,7 +45,15 @@ namespace {
 using namespace lk;
 
 constexpr int kL = RAFTCORR_MAX_LEVELS;           // the kernel is specialised for the 4-level pyramid
-constexpr int kWarps16 = 16;                       // per level: 2 unit buffers x a pair of warps
+#ifndef RAFTCORR_L16_SPLIT
+#define RAFTCORR_L16_SPLIT 1
+#endif
+#ifndef RAFTCORR_L16_UNROLL
+#define RAFTCORR_L16_UNROLL 2
+#endif
+constexpr int kUnroll16 = RAFTCORR_L16_UNROLL;     // unroll factor of the x-tap loop
+constexpr int kSplit16 = RAFTCORR_L16_SPLIT;       // warps per unit buffer (they split the x taps)
+constexpr int kWarps16 = 8 * kSplit16;             // per level: 2 unit buffers x kSplit16 warps
 constexpr int kThreads16 = kWarps16 * 32;
 constexpr int kDepth16 = 2;                        // unit buffers per level (each level runs its own ring)
 constexpr int kBufs = kL * kDepth16;
@@ -180,7 +191,7 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bh, 
     }
   }
   float* o = optr + (long long)(i_begin * rd) * N;
-#pragma unroll 2
+#pragma unroll kUnroll16
   for (int i = i_begin; i < i_end; ++i) {
     const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
     const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
@@ -254,7 +265,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   auto full_bar = [&](int b) { return smem_base + kOffBars16 + b * 8; };
 
   if (threadIdx.x < kBufs) {
-    mbar_init(full_bar(threadIdx.x), 2);    // one arrive.expect_tx per warp of the pair (+ the bytes of its 16 boxes)
+    mbar_init(full_bar(threadIdx.x), kSplit16);   // one arrive.expect_tx per warp of the pair (+ the bytes of its boxes)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -263,7 +274,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   const int n_tiles = (int)((p.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);   // tiles of this CTA
 
   // warp pair = one unit buffer: pairs 2l, 2l+1 belong to level l and take alternate tiles
-  const int pair = warp >> 1, h = warp & 1;
+  const int pair = warp / kSplit16, h = warp % kSplit16;
   const int level = pair >> 1, first = pair & 1;
   const Level16Dev lv = p.lv[level];
   const uint32_t slot_addr = smem_base + pair * kBufBytes + (uint32_t)slot_of(lane, level) * kSlot;
@@ -330,10 +341,9 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     }
   };
   // this warp requests the boxes of lanes 16h .. 16h+15 of the pair's next unit
-  auto issue = [&](const Unit& u) {
-    const Window w = window_of<R, kMode>(u.cxl, u.cyl, lv);
+  auto issue = [&](const Unit& u, const Window& w) {
     const int bw = 2 + w.wide, bh = 3 + w.tall;
-    const uint32_t bytes = (u.live && w.fast && (lane >> 4) == h) ? (uint32_t)(bw * bh * 64) : 0u;
+    const uint32_t bytes = (u.live && w.fast && (kSplit16 == 1 || (lane >> 4) == h)) ? (uint32_t)(bw * bh * 64) : 0u;
     const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
     if (lane == 0) mbar_expect_tx(bar, total);
     __syncwarp();
@@ -343,7 +353,6 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
       tma_load_4d(slot_addr, &maps.m[level][w.wide][w.tall], bar, 0, bx, by, (int)u.img);
     }
   };
-
   if (first >= n_tiles) return;
   float ncx, ncy;
   Cursor cu = cursor_at(first);            // the unit about to be fetched / sampled
@@ -358,7 +367,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     const unsigned steps = (p.debug >> 8) ? (unsigned)(p.debug >> 8) : 4u;
     for (unsigned t = 0; t < steps && steps != 255u; ++t) __nanosleep(256);
   }
-  issue(cur);
+  issue(cur, window_of<R, kMode>(cur.cxl, cur.cyl, lv));
   load_coords(cc, first + kDepth16 < n_tiles, ncx, ncy);
   advance(cc);                             // -> first + 4
   uint32_t phase = 0;
@@ -366,6 +375,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     const bool more = k + kDepth16 < n_tiles;
     Unit nxt = cur;
     if (more) nxt = unit_at(cu, ncx, ncy);
+    const Window wn = window_of<R, kMode>(nxt.cxl, nxt.cyl, lv);
     advance(cu);
     load_coords(cc, k + 2 * kDepth16 < n_tiles, ncx, ncy);   // two units ahead
     advance(cc);
@@ -396,7 +406,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     mbar_wait(bar, phase, 2);
     phase ^= 1u;
     const bool all_flips = __all_sync(0xffffffffu, flips_ok || !live);
-    const int ib = h ? kMid : 0, ie = h ? rd : kMid;
+    const int ib = (kSplit16 == 2 && h) ? kMid : 0, ie = (kSplit16 == 2 && !h) ? kMid : rd;
     if (p.debug & 1) {
     } else if (!all_fast || !all_flips) {
       // a window that does not fit a box (|coords| beyond ~2^20) or an irregular tap pattern somewhere in the warp:
@@ -411,8 +421,9 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     }
     if (more) {
       // both warps of the pair are done reading the buffer before either refills it
-      asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
-      issue(nxt);
+      if (kSplit16 == 2) asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
+      else __syncwarp();
+      issue(nxt, wn);
     }
     cur = nxt;
   }
