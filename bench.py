@@ -330,6 +330,24 @@ def measure_other_configs(dev, hbm_peak_gbs, model=None, frames=None):
     out["train_cfg5"] = {"workload": "CorrBlock build + 12 lookups, forward and backward, 368x496 (46x62 fmaps), batch 12",
                          "ms_per_step": timed(train_step, reps=3, warm=1)}
     del f1, f2
+    # configs[4] as written, on this one GPU: the whole training step of the unmodified reference model (forward, loss,
+    # backward, clip, AdamW step; harness/train_step.py) with this library's corr.py and with the reference's own
+    from harness import ref_model as _rm, train_step as _ts
+    if _rm.available():
+        def whole_step(dropin):
+            tr = _ts.Trainer(dev, dropin=dropin)
+            batch = _ts.synthetic_batch(_ts.BATCH_PER_GPU, dev, seed=500)
+            ms = timed(lambda: tr.step(*batch), reps=3, warm=2)
+            del tr
+            torch.cuda.empty_cache()
+            return ms
+        ours_ms, theirs_ms = whole_step(True), whole_step(False)
+        out["train_step_cfg5"] = {
+            "workload": "unmodified reference RAFT, whole training step, 368x496, batch 12, 12 iterations, 1 GPU "
+                        "(python bench.py --workload train under torchrun gives the N-GPU DDP line)",
+            "ms_per_step": ours_ms, "frame_pairs_per_s": _ts.BATCH_PER_GPU / (ours_ms * 1e-3),
+            "corr_fwd_bwd_share_of_step": out["train_cfg5"]["ms_per_step"] / ours_ms,
+            "same_step_with_reference_corr_py_ms": theirs_ms}
     # configs[2]: KITTI shape, 47x156 fmaps, batch 16, 24 iterations: the correlation path alone
     B, D, H, W = 16, 256, 47, 156
     f1 = torch.randn(B, D, H, W, device=dev, generator=gen)
@@ -400,12 +418,79 @@ def measure_other_configs(dev, hbm_peak_gbs, model=None, frames=None):
     return out
 
 
+def run_train_workload(args, rank: int, world: int, local_rank: int):
+    """BASELINE.json configs[4]: whole training step (harness/train_step.py), one process per GPU, NCCL all-reduce
+    through DistributedDataParallel.  Not the headline metric: printed as its own JSON line."""
+    from harness import ref_model, train_step
+    if not ref_model.available():
+        if rank == 0:
+            emit({"workload": "train_cfg5", "unavailable": "baseline/_ref not installed (tools/install_ref.py)"})
+        return
+    distributed = world > 1
+    if distributed:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank if distributed else 0)
+    torch.cuda.set_device(dev)
+    steps, warmup = args.steps, max(args.warmup, 3)
+
+    def measure(dropin: bool):
+        tr = train_step.Trainer(dev, dropin=dropin, distributed=distributed, local_rank=local_rank,
+                                precision=args.precision)
+        batch = train_step.synthetic_batch(train_step.BATCH_PER_GPU, dev, seed=500 + rank)
+        for _ in range(warmup):
+            tr.step(*batch)
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(steps):
+            loss, _ = tr.step(*batch)
+        t1.record()
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
+        if distributed:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        peak_gb = torch.cuda.max_memory_allocated(dev) / 2 ** 30
+        del tr
+        torch.cuda.empty_cache()
+        torch.cuda.reset_peak_memory_stats(dev)
+        return float(ms.item()) / steps, float(loss.item()), peak_gb
+
+    ours_ms, ours_loss, ours_gb = measure(True)
+    ref_ms = ref_loss = ref_gb = None
+    if not args.skip_cpu_baseline:       # the same step with the reference's own corr.py (ATen ops) on the same GPUs
+        ref_ms, ref_loss, ref_gb = measure(False)
+    if rank == 0:
+        pairs = train_step.BATCH_PER_GPU * world
+        emit({"workload": "train_cfg5", "metric": "RAFT training step frame-pairs/s @368x496 12 iters (BASELINE.json configs[4])",
+              "value": pairs / (ours_ms * 1e-3), "unit": "frame-pairs/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+              "ms_per_step": ours_ms, "higher_is_better": True, "scaling": "weak", "dtype": args.precision or "bf16",
+              "data": "synthetic",
+              "config": {"workload": "unmodified reference RAFT (baseline/_ref) forward + sequence_loss + backward + clip + "
+                                     "AdamW/OneCycle step, 368x496, batch 12 per GPU, 12 iterations, fp32 networks",
+                         "corr": "this library's CorrBlock (fp32 pyramid for gradients) and autograd kernels",
+                         "gradient_allreduce": "DistributedDataParallel over NCCL" if distributed else "single GPU, none"},
+              "loss_after_timed_steps": ours_loss, "peak_memory_gib": ours_gb,
+              "same_step_with_reference_corr_py": None if ref_ms is None else
+              {"ms_per_step": ref_ms, "frame_pairs_per_s": pairs / (ref_ms * 1e-3), "loss_after_timed_steps": ref_loss,
+               "peak_memory_gib": ref_gb}})
+    if distributed:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="infer", choices=["infer", "train"],
+                    help="infer: the headline metric (configs[1]); train: configs[4], whole training step under DDP")
     ap.add_argument("--precision", default=None, help="bf16 (default) | tf32 | fp32 for the volume build")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--tc-convc1", action="store_true",
@@ -446,6 +531,8 @@ def main():
         return
 
     assert torch.cuda.is_available(), "bench.py (impl ours) needs CUDA devices; there is no CPU fallback"
+    if args.workload == "train":
+        return run_train_workload(args, rank, world, local_rank)
     import corr as raftcorr_dropin  # the drop-in module; raises if libraftcorr_b200.so is missing
 
     distributed = world > 1
