@@ -759,11 +759,11 @@ def main():
         "clocks": clocks,
     }
     if n_gpus == 1:
-        line["dropin_unchanged"] = measure_dropin_unchanged(dev, (dev1, dev2))
-        line["measured_here"] = measure_tf32_peak(dev)
         line["other_configs"] = measure_other_configs(dev, peak, model, (dev1, dev2))
         if "latency_batch1" in line["other_configs"]:
             line["latency_batch1"] = line["other_configs"]["latency_batch1"]
+        line["dropin_unchanged"] = measure_dropin_unchanged(dev, (dev1, dev2))
+        line["measured_here"] = measure_tf32_peak(dev)      # last: a seconds-long GEMM burn pulls the clocks down
     if not args.skip_cpu_baseline and n_gpus == 1:
         ref = run_cpu_reference(steps=1, warmup=1)
         line["cpu_baseline"] = {"value": ref["value"], "unit": UNIT, "cores": ref["cores"], "kind": ref["kind"],
