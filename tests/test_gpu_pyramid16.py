@@ -152,6 +152,23 @@ def test_lookup16_wild_coordinates():
     assert np.array_equal(np.nan_to_num(out, nan=0.0), np.nan_to_num(ref, nan=0.0))
 
 
+def test_lookup16_unit_whose_boxes_exceed_the_buffer():
+    """Every query looking at the same spot, placed so that every level-0 window needs the largest box (3 x 4
+    blocks): the 32 boxes of a unit do not fit its packed buffer and the kernel samples that unit from global
+    memory instead.  Same bit-exact bar."""
+    B, H, W = 2, 24, 64
+    gen = torch.Generator().manual_seed(77)
+    levels = [torch.randn(B * H * W, 1, H >> l, W >> l, generator=gen) for l in range(4)]
+    pyr = ops.Pyramid16.from_dense(levels, B, H, W)
+    c = torch.empty(B, 2, H, W)
+    c[:, 0] = 11.5      # x_lo = 7: the window straddles three block columns
+    c[:, 1] = 7.5       # y_lo = 3: ... and four block rows
+    c[1] += 0.25 * torch.randn(2, H, W, generator=gen).clamp(-1, 1) * 0.1
+    out = ops.lookup(pyr, c.cuda(), 4, "aten_cpu").cpu().numpy()
+    ref = oracle.lookup(_levels_numpy(pyr), c.numpy(), 4)
+    assert np.array_equal(out, ref)
+
+
 @pytest.mark.parametrize("shape", [(8, 55, 128), (4, 47, 156)])
 def test_full_size_build16_and_lookup16(shape):
     """BASELINE.json configs[1] / configs[2] shapes, D=256: the 16-bit build against the fp32-pyramid build
