@@ -152,10 +152,9 @@ def test_lookup16_wild_coordinates():
     assert np.array_equal(np.nan_to_num(out, nan=0.0), np.nan_to_num(ref, nan=0.0))
 
 
-def test_lookup16_unit_whose_boxes_exceed_the_buffer():
+def test_lookup16_every_window_needs_the_largest_box():
     """Every query looking at the same spot, placed so that every level-0 window needs the largest box (3 x 4
-    blocks): the 32 boxes of a unit do not fit its packed buffer and the kernel samples that unit from global
-    memory instead.  Same bit-exact bar."""
+    blocks = a whole 768-byte slot, for all 32 lanes of a unit at once).  Same bit-exact bar."""
     B, H, W = 2, 24, 64
     gen = torch.Generator().manual_seed(77)
     levels = [torch.randn(B * H * W, 1, H >> l, W >> l, generator=gen) for l in range(4)]
