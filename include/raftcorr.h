@@ -101,7 +101,13 @@ int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B
  *      DRAM granules.  Here every level holds bfloat16 pixels in blocks of 4 rows x 8 columns = 64 bytes (one
  *      DRAM granule; a 10x10 window touches ~7 of them instead of ~13 row pieces):
  *        pixel (y, x) of image n lives at byte  n*image_stride + ((y>>2)*blocks_x + (x>>3))*64 + (y&3)*16 + (x&7)*2
- *      with blocks_x = ceil(W/8), blocks_y = ceil(H/4), image_stride = blocks_x*blocks_y*64.  Pixels of a block
+ *      with blocks_x = ceil(W/8), blocks_y = ceil(H/4), image_stride = blocks_x*blocks_y*64.
+ *      A level may keep the blocks of G = 2^interleave_log2 neighbouring images side by side (image n = b*H*W +
+ *      y*W + x, so neighbours are neighbouring queries of a row, whose windows nearly coincide: the lookup fetches
+ *      them as one box, and DRAM then sees pieces of G*128..192 bytes instead of G pieces 14 KB apart):
+ *        byte  (n / G) * G*image_stride + (((y>>2)*blocks_x + (x>>3)) * G + n % G) * 64 + (y&3)*16 + (x&7)*2
+ *      raftcorr_pyramid16_layout chooses it (levels 0 and 1, when H*W is a multiple of G); the lookup takes
+ *      either form per level, the build takes interleave_log2 in {0, 2} on levels 0 and 1 and 0 on the others.  Pixels of a block
  *      that lie outside the H x W image are stored as +0.0 (the lookup relies on it: they are grid_sample's zero
  *      padding).  Values: bf16 tcgen05 products, fp32 accumulation and pooling, one rounding to bf16 per stored
  *      pixel: <= 1e-2 of max|ref| like RAFTCORR_PREC_BF16.  Inference only (gradients use the fp32 pyramid). */
@@ -109,7 +115,9 @@ typedef struct raftcorr_level16 {
   void* data;           /* bfloat16, 64-byte aligned                    */
   int32_t H, W;         /* pixels                                       */
   int32_t blocks_x, blocks_y;
-  int64_t image_stride; /* bytes between images = blocks_x*blocks_y*64  */
+  int32_t interleave_log2; /* g: the blocks of 2^g neighbouring images are interleaved (see above); 0 = not */
+  int32_t reserved;        /* 0 */
+  int64_t image_stride; /* bytes of one image = blocks_x*blocks_y*64   */
 } raftcorr_level16;
 /* Fills H/W/blocks_x/blocks_y/image_stride of levels[0..L) (data untouched); bytes_per_level[l] = B*H*W images. */
 int raftcorr_pyramid16_layout(int B, int H, int W, int num_levels, raftcorr_level16* levels,

@@ -44,6 +44,7 @@ int launch_build_tc_noalloc(const float* f1, const float* f2, int B, int D, int 
                             const raftcorr_level* levels, int precision, cudaStream_t stream);
 int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int W, int L,
                       const raftcorr_level16* levels, void* ws, int64_t ws_bytes, cudaStream_t stream);
+int lookup16_group_log2(int level);   // lookup16.cu: the lookup fetches the windows of 2^g neighbouring queries as one box
 int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coords, float* out, int B, int H, int W,
                         int r, int mode, cudaStream_t stream);
 int64_t build_bwd_workspace_bytes(int B, int D, int H, int W);
@@ -99,6 +100,10 @@ static int check_levels16(const raftcorr_level16* levels, int L, int H, int W, c
                v.blocks_x, v.blocks_y, v.W, v.H);
     RC_REQUIRE(v.image_stride >= (int64_t)v.blocks_x * v.blocks_y * 64 && !(v.image_stride & 63),
                "%s: levels[%d].image_stride must be a multiple of 64 and >= blocks_x*blocks_y*64", what, l);
+    RC_REQUIRE(v.interleave_log2 >= 0 && v.interleave_log2 <= 3, "%s: levels[%d].interleave_log2=%d not in [0,3]", what, l,
+               v.interleave_log2);
+    RC_REQUIRE(v.interleave_log2 == 0 || v.image_stride == (int64_t)v.blocks_x * v.blocks_y * 64,
+               "%s: levels[%d]: an interleaved level needs image_stride == blocks_x*blocks_y*64", what, l);
   }
   return 0;
 }
@@ -197,6 +202,10 @@ int raftcorr_pyramid16_layout(int B, int H, int W, int num_levels, raftcorr_leve
     levels[l].blocks_x = (Wl + 7) / 8;
     levels[l].blocks_y = (Hl + 3) / 4;
     levels[l].image_stride = (int64_t)levels[l].blocks_x * levels[l].blocks_y * 64;
+    // levels 0 and 1 (images of several KB, windows = a few 128..192-byte pieces of them) keep the blocks of the
+    // 2^g queries the lookup fetches together side by side: one DRAM piece of 2^g * 128..192 bytes instead of 2^g
+    levels[l].interleave_log2 = (l < 2 && ((long long)H * W) % (1 << lookup16_group_log2(l)) == 0) ? lookup16_group_log2(l) : 0;
+    levels[l].reserved = 0;
     bytes_per_level[l] = (int64_t)B * H * W * levels[l].image_stride;
   }
   return 0;

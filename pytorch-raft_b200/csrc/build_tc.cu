@@ -58,6 +58,7 @@ struct BuildTcParams {
   int bxs[RAFTCORR_MAX_LEVELS], bys[RAFTCORR_MAX_LEVELS];
   unsigned char* l3_data;
   long long l3_istride;   // bytes
+  int ilog[2];            // levels 0, 1: log2 of the number of neighbouring images whose blocks are interleaved (0: none)
 };
 
 // Stage one row segment (kNF floats per query, 32 queries) in swizzled shared memory and hand it
@@ -107,6 +108,29 @@ __device__ __forceinline__ uint32_t stage16_begin(uint32_t buf_base, uint32_t& n
   __syncwarp();
   return buf;
 }
+// Interleaved levels (raftcorr_level16.interleave_log2 = g >= 1): memory is [group of 2^g images][block row][block]
+// [image][64 B].  The blocks of two neighbouring images are one 128-byte row of the tensor map (64-byte rows halve
+// the store engine's throughput), so a staged box is {128 B, 2^(g-1) image pairs, 2 blocks, 1 block row, 32 >> g
+// groups} with SWIZZLE_128B (16-byte chunk index ^= 128-byte row index & 7; the staging buffers are 1 KB aligned).
+// Chunk r of block bl of the lane's query:
+__device__ __forceinline__ void stage16_chunk_il(uint32_t buf, int lane, int ilog, int bl, int r, uint32_t a, uint32_t b,
+                                                 uint32_t cc, uint32_t d) {
+  const int m = lane & ((1 << ilog) - 1);   // image within its group
+  const uint32_t row = ((uint32_t)(lane >> ilog) << ilog) + ((uint32_t)bl << (ilog - 1)) + (uint32_t)(m >> 1);
+  const uint32_t phys = (uint32_t)((m & 1) * 4 + r) ^ (row & 7u);
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf + row * 128 + phys * 16), "r"(a), "r"(b), "r"(cc), "r"(d)
+               : "memory");
+}
+// one box for the warp's 32 queries or, in a tile that ends before them (N % 32 != 0), one per live group
+__device__ __forceinline__ void store16_il(const CUtensorMap* map, const CUtensorMap* map_tail, uint32_t buf, int ilog,
+                                           int bx, int by, long long image0, int live) {
+  const int g0 = (int)(image0 >> ilog);
+  if (live >= 32) {
+    tma_store_5d(map, buf, 0, 0, bx, by, g0);
+  } else {
+    for (int g = 0; (g << ilog) < live; ++g) tma_store_5d(map_tail, buf + ((uint32_t)g << (7 + ilog)), 0, 0, bx, by, g0 + g);
+  }
+}
 template <int kRowBytes>
 __device__ __forceinline__ void stage16_chunk(uint32_t buf, int lane, int c, uint32_t a, uint32_t b, uint32_t cc,
                                               uint32_t d) {
@@ -123,6 +147,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
                 const __grid_constant__ CUtensorMap mapL0, const __grid_constant__ CUtensorMap mapL1,
                 const __grid_constant__ CUtensorMap mapL2, const __grid_constant__ CUtensorMap mapL3,
+                const __grid_constant__ CUtensorMap mapL0t, const __grid_constant__ CUtensorMap mapL1t,
                 const __grid_constant__ BuildTcParams p) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const uint32_t smem_base = smem_u32(smem);
@@ -301,12 +326,14 @@ build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
 #pragma unroll
                   for (int r = 0; r < 4; ++r) {
                     const uint32_t* src = (r < 2 ? prev : cur) + (r & 1) * 16 + (2 * h + bl) * 4;
-                    stage16_chunk<128>(buf, lane, bl * 4 + r, src[0], src[1], src[2], src[3]);
+                    if (p.ilog[0]) stage16_chunk_il(buf, lane, p.ilog[0], bl, r, src[0], src[1], src[2], src[3]);
+                    else stage16_chunk<128>(buf, lane, bl * 4 + r, src[0], src[1], src[2], src[3]);
                   }
                 fence_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                  tma_store_4d(&mapL0, buf, bx * 32, by, q0, b);
+                  if (p.ilog[0]) store16_il(&mapL0, &mapL0t, buf, p.ilog[0], bx, by, (long long)b * p.N + q0, p.N - q0);
+                  else tma_store_4d(&mapL0, buf, bx * 32, by, q0, b);
                   bulk_commit();
                 }
               }
@@ -333,12 +360,14 @@ build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
               const uint32_t* src = l1pk + r * 8 + bl * 4;
-              stage16_chunk<128>(buf, lane, bl * 4 + r, src[0], src[1], src[2], src[3]);
+              if (p.ilog[1]) stage16_chunk_il(buf, lane, p.ilog[1], bl, r, src[0], src[1], src[2], src[3]);
+              else stage16_chunk<128>(buf, lane, bl * 4 + r, src[0], src[1], src[2], src[3]);
             }
           fence_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_4d(&mapL1, buf, 2 * tx * 32, ty, q0, b);
+            if (p.ilog[1]) store16_il(&mapL1, &mapL1t, buf, p.ilog[1], 2 * tx, ty, (long long)b * p.N + q0, p.N - q0);
+            else tma_store_4d(&mapL1, buf, 2 * tx * 32, ty, q0, b);
             bulk_commit();
           }
         }
@@ -562,7 +591,8 @@ int64_t build_tc_workspace_bytes(int B, int D, int H, int W, int precision) {
 
 // Shared launcher of build_tc_kernel: operand maps for `passes` (A, B) pairs are already encoded.
 static int launch_tc_kernel(bool tf32, const TcOperandMaps& ops, const CUtensorMap* out_maps, const BuildTcParams& p,
-                            cudaStream_t stream, bool out16 = false) {
+                            cudaStream_t stream, bool out16 = false, const CUtensorMap* tail_maps = nullptr) {
+  if (tail_maps == nullptr) tail_maps = out_maps;   // (only the interleaved 16-bit epilogue uses them)
   int dev = 0, sms = 0;
   RC_CHECK_CUDA(cudaGetDevice(&dev));
   RC_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -571,13 +601,13 @@ static int launch_tc_kernel(bool tf32, const TcOperandMaps& ops, const CUtensorM
   const int grid = (int)(total < sms ? total : sms);
   if (out16) {
     RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<false, true><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
+    build_tc_kernel<false, true><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
   } else if (!tf32) {
     RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<false, false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
+    build_tc_kernel<false, false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
   } else {
     RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<true, false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], p);
+    build_tc_kernel<true, false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
   }
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -665,6 +695,7 @@ int launch_build_tc(const float* f1, const float* f2, int B, int D, int H, int W
   }
 
   BuildTcParams p;
+  p.ilog[0] = p.ilog[1] = 0;
   p.B = B;
   p.N = N;
   p.H = H;
@@ -726,8 +757,24 @@ int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int
       if (int rc = encode(&ops.b[ps], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, packB, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "B")) return rc;
     }
   }
-  CUtensorMap mapL[RAFTCORR_MAX_LEVELS];
+  CUtensorMap mapL[RAFTCORR_MAX_LEVELS], mapT[2];
   for (int l = 0; l < 2; ++l) {   // levels 0, 1: two whole blocks (128 B) per query per box
+    if (l < L && levels[l].interleave_log2 > 0) {
+      // [group of 2^g images][block row][block][image][64 B]: one box = 2 blocks of the warp's 32 queries
+      const raftcorr_level16& lv = levels[l];
+      const int g = lv.interleave_log2;
+      if (N % (1 << g) != 0 || g > 3 || g < 1)
+        return fail(RAFTCORR_E_UNSUPPORTED, "build_pyramid16: level %d interleaves 2^%d images, H*W=%d is not a multiple", l, g, N);
+      cuuint64_t dims[5] = {64, 1ull << (g - 1), (cuuint64_t)lv.blocks_x, (cuuint64_t)lv.blocks_y, ((cuuint64_t)B * N) >> g};
+      cuuint64_t strides[4] = {128, 64ull << g, (cuuint64_t)lv.blocks_x * (64ull << g), (cuuint64_t)lv.image_stride << g};
+      cuuint32_t box[5] = {64, 1u << (g - 1), 2, 1, 32u >> g};
+      if (int rc = encode(&mapL[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, lv.data, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "level16 interleaved"))
+        return rc;
+      box[4] = 1;
+      if (int rc = encode(&mapT[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, lv.data, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "level16 interleaved, one group"))
+        return rc;
+      continue;
+    }
     // A block row of an image is contiguous (blocks_x * 64 B), so the two innermost axes (pixel in block, block
     // column) are one axis of blocks_x * 32 elements: the box's inner row is then exactly the 128-byte swizzle span
     // (a 64-byte inner axis would be padded to 128-byte rows in shared memory: tools/probe/tma_swizzle_probe.cu),
@@ -738,7 +785,11 @@ int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int
     cuuint32_t box[4] = {64, 1, 32, 1};
     if (int rc = encode(&mapL[l], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, lv.data, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B, "level16"))
       return rc;
+    mapT[l] = mapL[l];
   }
+  for (int l = 2; l < L; ++l)
+    if (levels[l].interleave_log2 != 0)
+      return fail(RAFTCORR_E_UNSUPPORTED, "build_pyramid16: only levels 0 and 1 may be interleaved (level %d)", l);
   {                               // level 2: 32-byte half blocks (rows 0-1 / 2-3 of a block), one per query per box
     const raftcorr_level16& lv = levels[2 < L ? 2 : 0];
     cuuint64_t dims[4] = {16, (cuuint64_t)lv.blocks_x * lv.blocks_y * 2, (cuuint64_t)N, (cuuint64_t)B};
@@ -750,6 +801,7 @@ int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int
   }
 
   BuildTcParams p;
+  p.ilog[0] = p.ilog[1] = 0;
   p.B = B;
   p.N = N;
   p.H = H;
@@ -775,7 +827,9 @@ int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int
   }
   p.l3_data = L > 3 ? static_cast<unsigned char*>(levels[3].data) : nullptr;
   p.l3_istride = L > 3 ? levels[3].image_stride : 0;
-  return launch_tc_kernel(false, ops, mapL, p, stream, true);
+  p.ilog[0] = levels[0].interleave_log2;
+  p.ilog[1] = L > 1 ? levels[1].interleave_log2 : 0;
+  return launch_tc_kernel(false, ops, mapL, p, stream, true, mapT);
 }
 
 // Batched fp32-accurate GEMM on the tf32 tensor pipe (plain epilogue), used by build_bwd.cu:
@@ -824,6 +878,7 @@ int launch_tc_gemm_any(const float* const* a_src, const float* const* b_src, int
         return rc;
   }
   BuildTcParams p;
+  p.ilog[0] = p.ilog[1] = 0;
   p.B = B;
   p.N = M;     // rows of C (TMEM lanes)
   p.H = 1;

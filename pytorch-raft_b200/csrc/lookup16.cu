@@ -57,17 +57,43 @@ constexpr int kWarps16 = 8 * kSplit16;             // per level: 2 unit buffers 
 constexpr int kThreads16 = kWarps16 * 32;
 constexpr int kDepth16 = 2;                        // unit buffers per level (each level runs its own ring)
 constexpr int kBufs = kL * kDepth16;
-constexpr int kSlot = 896;                         // 7 x 128 B >= the largest box (3 x 4 blocks = 768 B)
-constexpr int kBufBytes = 32 * kSlot;              // 28 KB: a multiple of 1024, so swizzle phases are slot-relative
+constexpr int kBoxMax = 768;                       // the largest box of one query: 3 x 4 blocks
+constexpr int kSlot = kBoxMax + 128;               // slot pitch of ungrouped queries: an odd multiple of 128 B
+constexpr int kBufBytes = 32 * kSlot;              // 28 KB
+// Queries whose images are neighbours in memory (consecutive x) and whose windows share one block-aligned box are
+// fetched by ONE tensor box over 2^g images: a warp issues a box only every ~70 cycles (the operands travel
+// through uniform registers, one elected lane at a time), and 32 boxes per unit were a quarter of a unit's time.
+// Group size per level, log2 (neighbouring queries are 1, 1/2, 1/4, 1/8 level pixel apart):
+#ifndef RAFTCORR_L16_GROUPS
+#define RAFTCORR_L16_GROUPS 0x2222
+#endif
+constexpr int kGroups16 = RAFTCORR_L16_GROUPS;     // hex digit l = log2 of the group size at level l (0..3)
+__host__ __device__ constexpr int group_log2(int level) { return (kGroups16 >> (4 * level)) & 15; }
+// a group's region: its queries' boxes back to back (pitch = the box bytes) or, ungrouped, at kBoxMax; the region
+// pitch is an odd multiple of 128 B so that neighbouring groups start in different swizzle phases
+__host__ __device__ constexpr int group_pitch(int glog) { return (kBoxMax << glog) + 128; }
+static_assert((32 >> group_log2(0)) * group_pitch(group_log2(0)) <= kBufBytes && group_log2(0) <= 3, "level 0 groups");
+static_assert((32 >> group_log2(1)) * group_pitch(group_log2(1)) <= kBufBytes && group_log2(1) <= 3, "level 1 groups");
+static_assert((32 >> group_log2(2)) * group_pitch(group_log2(2)) <= kBufBytes && group_log2(2) <= 3, "level 2 groups");
+static_assert((32 >> group_log2(3)) * group_pitch(group_log2(3)) <= kBufBytes && group_log2(3) <= 3, "level 3 groups");
 constexpr int kOffBars16 = kBufs * kBufBytes;
 constexpr int kSmem16 = kOffBars16 + kBufs * 8;
 
 struct Level16Dev {
   const unsigned char* data;
   int H, W, bxs, bys;
-  long long istride;                                // bytes
+  int ilog;                                         // the blocks of 2^ilog neighbouring images are interleaved (0: not)
+  long long istride;                                // bytes of one image's blocks
   float sm1x, invx, halfx, sm1y, invy, halfy, inv_pow2;
 };
+
+#ifdef RAFTCORR_L16_TRACE
+// development build only (tools/trace16.py): cycles each warp spends per phase, summed over its units
+__device__ unsigned long long g_trace16[148 * 8 * 32];   // [SM][warp]: 4 phase sums, units, whole warp, -, -, then 8 rounds x (wait, sample, issue)
+#define L16_TICK(var) const long long var = clock64()
+#else
+#define L16_TICK(var)
+#endif
 
 struct Lookup16Params {
   Level16Dev lv[kL];
@@ -78,9 +104,9 @@ struct Lookup16Params {
   int debug;   // development switches (RAFTCORR_L16_DEBUG): bit 0 = skip the sampling (fill path only); bits 8.. = start skew
 };
 
-// box shapes: [level][wide: 2 or 3 blocks][tall: 3 or 4 block rows]
+// box shapes: [level][one image / the level's group of images][wide: 2 or 3 blocks][tall: 3 or 4 block rows]
 struct alignas(64) Lookup16Maps {
-  CUtensorMap m[kL][2][2];
+  CUtensorMap m[kL][2][2][2];
 };
 
 // slot of lane q in a unit buffer (a permutation of 0..31 per level; skew class = slot & 3): class mates are
@@ -98,6 +124,7 @@ struct Window {
   int bx0, by0;   // first block column / row of the box (may lie outside the image)
   int wide, tall; // 0/1: box is 2+wide blocks x 3+tall block rows
   int fast;       // all taps inside such a box (false only for |coords| so large that fp32 spacing breaks the pattern)
+  int grouped;    // bx0/by0/wide/tall describe the box shared by the lane's whole group
 };
 
 __device__ __forceinline__ Window window_from(int x_lo, int x_hi, int y_lo, int y_hi) {
@@ -108,6 +135,30 @@ __device__ __forceinline__ Window window_from(int x_lo, int x_hi, int y_lo, int 
   w.fast = (nbx >= 1) & (nbx <= 3) & (nby >= 1) & (nby <= 4);
   w.wide = nbx > 2;
   w.tall = nby > 3;
+  w.grouped = 0;
+  return w;
+}
+// the box that holds the windows of all 2^glog lanes of a group, if one of the four shapes does
+__device__ __forceinline__ Window group_window(Window w, bool usable, int glog) {
+  int x0 = w.bx0, y0 = w.by0, x1 = w.bx0 + 1 + w.wide, y1 = w.by0 + 2 + w.tall;
+  bool ok = usable && w.fast;
+#pragma unroll
+  for (int s = 0; s < 3; ++s)
+    if (s < glog) {
+      const int d = 1 << s;
+      x0 = min(x0, __shfl_xor_sync(0xffffffffu, x0, d));
+      y0 = min(y0, __shfl_xor_sync(0xffffffffu, y0, d));
+      x1 = max(x1, __shfl_xor_sync(0xffffffffu, x1, d));
+      y1 = max(y1, __shfl_xor_sync(0xffffffffu, y1, d));
+      ok = ok & (__shfl_xor_sync(0xffffffffu, (int)ok, d) != 0);
+    }
+  if (glog > 0 && ok && x1 - x0 <= 2 && y1 - y0 <= 3) {
+    w.bx0 = x0;
+    w.by0 = y0;
+    w.wide = x1 - x0 > 1;
+    w.tall = y1 - y0 > 2;
+    w.grouped = 1;
+  }
   return w;
 }
 // first and last tap decide the box (taps are monotone in their offset)
@@ -126,7 +177,8 @@ __device__ __forceinline__ float bf16_bits_to_float(uint32_t h) { return __uint_
 // rare path: straight from global memory, with bounds checks (zero padding)
 __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img, int y, int x) {
   if (x < 0 || y < 0 || x >= lv.W || y >= lv.H) return 0.0f;
-  const unsigned char* p = lv.data + img * lv.istride + ((long long)(y >> 2) * lv.bxs + (x >> 3)) * 64 + (y & 3) * 16 +
+  const long long member = img & ((1LL << lv.ilog) - 1), block = (long long)(y >> 2) * lv.bxs + (x >> 3);
+  const unsigned char* p = lv.data + (img - member) * lv.istride + ((block << lv.ilog) + member) * 64 + (y & 3) * 16 +
                            (x & 7) * 2;
   return bf16_bits_to_float(*reinterpret_cast<const unsigned short*>(p));
 }
@@ -144,11 +196,11 @@ __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img
 // the variants of this routine came to 10k SASS instructions and the warps of an SM — each in a different variant
 // or phase — spent 40 % of their issue slots waiting for the instruction cache.
 template <int R, int kMode, bool kFlips, bool kAllLive>
-__device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bh, int bx0, int by0, int mx, int my,
+__device__ __forceinline__ void sample_unit(uint32_t slot_addr, int cshift, int bw, int bh, int bx0, int by0, int mx, int my,
                                             float cxl, const Level16Dev& lv, const Tap (&ty)[2 * R + 1], int i_begin,
                                             int i_end, float* optr, long long N, bool live) {
   constexpr int rd = 2 * R + 1, kRows = rd + 1 + (kFlips ? 1 : 0);
-  const int rowpitch = bw * 64;   // bytes per block row of the box
+  const int rowpitch = bw << cshift;   // bytes per block row of the box (a block column is 1 << cshift bytes wide)
   auto px = [&](uint32_t row, uint32_t col) -> float {
     unsigned short v;
     asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz64(row + col)));
@@ -171,7 +223,7 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int bw, int bh, 
   auto col_off = [&](int c) {
     int xx = mx + c - 8 * bx0;
     if (kFlips) xx = max(0, min(xx, 8 * bw - 1));
-    return (uint32_t)((xx >> 3) * 64 + (xx & 7) * 2);
+    return (uint32_t)(((xx >> 3) << cshift) + (xx & 7) * 2);
   };
   float fy[rd], sy[rd];
   bool ey[rd];
@@ -277,7 +329,18 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   const int pair = warp / kSplit16, h = warp % kSplit16;
   const int level = pair >> 1, first = pair & 1;
   const Level16Dev lv = p.lv[level];
-  const uint32_t slot_addr = smem_base + pair * kBufBytes + (uint32_t)slot_of(lane, level) * kSlot;
+  const int glog = group_log2(level), gl = lane & ((1 << glog) - 1);
+  // region of the lane's group in the unit buffer
+  const uint32_t group_addr =
+      smem_base + pair * kBufBytes +
+      (glog == 0 ? (uint32_t)slot_of(lane, level) * kSlot : (uint32_t)(lane >> glog) * (uint32_t)group_pitch(glog));
+  // A group's box holds its images one after the other or, from an interleaved level, block by block
+  // ([block row][block][image][64 B]); ungrouped queries keep kBoxMax bytes each.
+  const int ilog = lv.ilog;
+  auto slot_of_window = [&](const Window& w) {
+    const uint32_t pitch = !w.grouped ? (uint32_t)kBoxMax : ilog ? 64u : (uint32_t)((2 + w.wide) * (3 + w.tall) * 64);
+    return group_addr + (uint32_t)gl * pitch;
+  };
   const uint32_t bar = full_bar(pair);
 
   struct Unit {
@@ -285,6 +348,9 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     long long img;
     float* optr;
     bool live;
+  };
+  auto group_usable = [&](const Unit& u) {   // interleaved: the lanes of a group must be one group in memory too
+    return u.live && (ilog == 0 || ((int)u.img & ((1 << glog) - 1)) == gl);
   };
   // Tile cursors advance incrementally (a pair steps through tiles blockIdx + k * gridDim, k = first, first + 2, ...):
   // decoding a tile index costs two integer divisions, ~50 instructions each time, for every lane.
@@ -343,14 +409,16 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   // this warp requests the boxes of lanes 16h .. 16h+15 of the pair's next unit
   auto issue = [&](const Unit& u, const Window& w) {
     const int bw = 2 + w.wide, bh = 3 + w.tall;
-    const uint32_t bytes = (u.live && w.fast && (kSplit16 == 1 || (lane >> 4) == h)) ? (uint32_t)(bw * bh * 64) : 0u;
+    uint32_t bytes = (u.live && w.fast && (kSplit16 == 1 || (lane >> 4) == h)) ? (uint32_t)(bw * bh * 64) : 0u;
+    if (w.grouped) bytes = gl == 0 ? bytes << glog : 0u;   // the group's first lane fetches for all of them
     const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
     if (lane == 0) mbar_expect_tx(bar, total);
     __syncwarp();
     if (bytes) {
       // windows entirely outside the image are all zeros wherever the box sits: clamp far-away origins
       const int bx = max(-8, min(w.bx0, lv.bxs + 8)), by = max(-8, min(w.by0, lv.bys + 8));
-      tma_load_4d(slot_addr, &maps.m[level][w.wide][w.tall], bar, 0, bx, by, (int)u.img);
+      const int member = (ilog && !w.grouped) ? ((int)u.img & ((1 << ilog) - 1)) : 0;
+      tma_load_5d(slot_of_window(w), &maps.m[level][w.grouped][w.wide][w.tall], bar, 0, member, bx, by, (int)u.img >> ilog);
     }
   };
   if (first >= n_tiles) return;
@@ -367,15 +435,21 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     const unsigned steps = (p.debug >> 8) ? (unsigned)(p.debug >> 8) : 4u;
     for (unsigned t = 0; t < steps && steps != 255u; ++t) __nanosleep(256);
   }
-  issue(cur, window_of<R, kMode>(cur.cxl, cur.cyl, lv));
+  Window w = group_window(window_of<R, kMode>(cur.cxl, cur.cyl, lv), group_usable(cur), glog);   // the box of `cur`
+  issue(cur, w);
   load_coords(cc, first + kDepth16 < n_tiles, ncx, ncy);
   advance(cc);                             // -> first + 4
   uint32_t phase = 0;
+#ifdef RAFTCORR_L16_TRACE
+  long long tr_prep = 0, tr_wait = 0, tr_sample = 0, tr_issue = 0, tr_units = 0;
+  const long long tr_begin = clock64();
+#endif
   for (int k = first; k < n_tiles; k += kDepth16) {
+    L16_TICK(t0);
     const bool more = k + kDepth16 < n_tiles;
     Unit nxt = cur;
     if (more) nxt = unit_at(cu, ncx, ncy);
-    const Window wn = window_of<R, kMode>(nxt.cxl, nxt.cyl, lv);
+    const Window wn = group_window(window_of<R, kMode>(nxt.cxl, nxt.cyl, lv), group_usable(nxt), glog);
     advance(cu);
     load_coords(cc, k + 2 * kDepth16 < n_tiles, ncx, ncy);   // two units ahead
     advance(cc);
@@ -387,8 +461,9 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
       tx[j] = make_tap_fast(cur.cxl, (float)(j - R), lv.sm1x, lv.invx, lv.halfx, kMode);
       if (j) chain &= (ty[j].i0 == ty[j - 1].i0 + 1) & (tx[j].i0 == tx[j - 1].i0 + 1);
     }
-    const Window w = window_from(tx[0].i0, tx[rd - 1].i0 + 1, ty[0].i0, ty[rd - 1].i0 + 1);   // = what issue() used
     const int bw = 2 + w.wide, bh = 3 + w.tall;
+    const uint32_t slot_addr = slot_of_window(w);
+    const int cshift = 6 + (w.grouped ? ilog : 0);
     // floor flips: is tap j on pixel m + j + e_j with e_j in {0,1}?
     int mx = tx[0].i0, my = ty[0].i0, hx = tx[0].i0, hy = ty[0].i0;
 #pragma unroll
@@ -403,7 +478,9 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     const bool all_fast = __all_sync(0xffffffffu, w.fast || !live);
     const bool all_chain = __all_sync(0xffffffffu, chain || !live);
     const bool all_live = __all_sync(0xffffffffu, live);
+    L16_TICK(t1);
     mbar_wait(bar, phase, 2);
+    L16_TICK(t2);
     phase ^= 1u;
     const bool all_flips = __all_sync(0xffffffffu, flips_ok || !live);
     const int ib = (kSplit16 == 2 && h) ? kMid : 0, ie = (kSplit16 == 2 && !h) ? kMid : rd;
@@ -413,12 +490,13 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
       // every lane samples straight from global memory
       if (live) sample_unit_global<R, kMode>(lv, cur.img, cur.cxl, cur.cyl, ib, ie, cur.optr, N);
     } else if (all_chain && all_live) {
-      sample_unit<R, kMode, false, true>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+      sample_unit<R, kMode, false, true>(slot_addr, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
     } else if (all_chain) {
-      sample_unit<R, kMode, false, false>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+      sample_unit<R, kMode, false, false>(slot_addr, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
     } else {
-      sample_unit<R, kMode, true, false>(slot_addr, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+      sample_unit<R, kMode, true, false>(slot_addr, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
     }
+    L16_TICK(t3);
     if (more) {
       // both warps of the pair are done reading the buffer before either refills it
       if (kSplit16 == 2) asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
@@ -426,7 +504,22 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
       issue(nxt, wn);
     }
     cur = nxt;
+    w = wn;
+#ifdef RAFTCORR_L16_TRACE
+    const long long t4 = clock64();
+    if (lane == 0 && blockIdx.x < 148 && warp < 8 && tr_units < 8) {
+      unsigned long long* t = g_trace16 + ((size_t)blockIdx.x * 8 + warp) * 32 + 8 + tr_units * 3;
+      t[0] = t2 - t1, t[1] = t3 - t2, t[2] = t4 - t3;
+    }
+    tr_prep += t1 - t0, tr_wait += t2 - t1, tr_sample += t3 - t2, tr_issue += t4 - t3, tr_units += 1;
+#endif
   }
+#ifdef RAFTCORR_L16_TRACE
+  if (lane == 0 && blockIdx.x < 148 && warp < 8) {
+    unsigned long long* t = g_trace16 + ((size_t)blockIdx.x * 8 + warp) * 32;
+    t[0] = tr_prep, t[1] = tr_wait, t[2] = tr_sample, t[3] = tr_issue, t[4] = tr_units, t[5] = clock64() - tr_begin;
+  }
+#endif
 }
 
 // Tensor maps depend only on (pointers, sizes, strides); RAFT calls the lookup once per refinement iteration on the
@@ -435,7 +528,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
 struct MapKey16 {
   const void* data[kL];
   long long istride[kL], bn;
-  int bxs[kL], bys[kL];
+  int bxs[kL], bys[kL], ilog[kL];
 };
 constexpr int kMapCache16 = 8;
 struct MapCache16 {
@@ -469,6 +562,8 @@ int launch16(const Lookup16Params& p, const Lookup16Maps& maps, cudaStream_t str
 
 }  // namespace
 
+int lookup16_group_log2(int level) { return level >= 0 && level < kL ? group_log2(level) : 0; }
+
 int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coords, float* out, int B, int H, int W,
                         int r, int mode, cudaStream_t stream) {
   if (L != kL || (r != 3 && r != 4))
@@ -489,6 +584,10 @@ int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coor
     d.bxs = s.blocks_x;
     d.bys = s.blocks_y;
     d.istride = s.image_stride;
+    d.ilog = s.interleave_log2;
+    if (d.ilog != 0 && d.ilog != group_log2(l))
+      return fail(RAFTCORR_E_UNSUPPORTED, "lookup16_fwd: level %d interleaves 2^%d images, this build fetches groups of 2^%d",
+                  l, d.ilog, group_log2(l));
     d.sm1x = (float)(s.W - 1);
     d.invx = 1.0f / d.sm1x;
     d.halfx = d.sm1x / 2.0f;
@@ -500,6 +599,7 @@ int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coor
     key.istride[l] = s.image_stride;
     key.bxs[l] = s.blocks_x;
     key.bys[l] = s.blocks_y;
+    key.ilog[l] = s.interleave_log2;
   }
   Lookup16Maps maps;
   bool hit = false;
@@ -515,15 +615,23 @@ int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coor
   }
   if (!hit) {
     for (int l = 0; l < kL; ++l) {
-      cuuint64_t dims[4] = {32, (cuuint64_t)levels[l].blocks_x, (cuuint64_t)levels[l].blocks_y, (cuuint64_t)BN};
-      cuuint64_t strides[3] = {64, (cuuint64_t)levels[l].blocks_x * 64, (cuuint64_t)levels[l].image_stride};
-      for (int wide = 0; wide < 2; ++wide)
-        for (int tall = 0; tall < 2; ++tall) {
-          cuuint32_t box[4] = {32, (cuuint32_t)(2 + wide), (cuuint32_t)(3 + tall), 1};
-          if (int rc = encode(&maps.m[l][wide][tall], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, levels[l].data, dims, strides,
-                              box, CU_TENSOR_MAP_SWIZZLE_64B, "lookup16 window", CU_TENSOR_MAP_L2_PROMOTION_NONE))
-            return rc;
-        }
+      // (64-byte block, image within its interleaved group, block column, block row, image or group of images)
+      const int ilog = levels[l].interleave_log2, G = 1 << group_log2(l);
+      const cuuint64_t members = 1ull << ilog, bstride = 64ull << ilog;
+      cuuint64_t dims[5] = {32, members, (cuuint64_t)levels[l].blocks_x, (cuuint64_t)levels[l].blocks_y,
+                            (cuuint64_t)((BN + (long long)members - 1) >> ilog)};
+      cuuint64_t strides[4] = {64, bstride, (cuuint64_t)levels[l].blocks_x * bstride,
+                               (cuuint64_t)levels[l].image_stride << ilog};
+      for (int grouped = 0; grouped < 2; ++grouped)
+        for (int wide = 0; wide < 2; ++wide)
+          for (int tall = 0; tall < 2; ++tall) {
+            cuuint32_t box[5] = {32, 1, (cuuint32_t)(2 + wide), (cuuint32_t)(3 + tall), 1};
+            if (grouped) box[ilog ? 1 : 4] = (cuuint32_t)G;
+            if (box[4] > dims[4]) box[4] = (cuuint32_t)dims[4];   // (never used then: a group needs 2^g live queries)
+            if (int rc = encode(&maps.m[l][grouped][wide][tall], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, levels[l].data, dims,
+                                strides, box, CU_TENSOR_MAP_SWIZZLE_64B, "lookup16 window", CU_TENSOR_MAP_L2_PROMOTION_NONE))
+              return rc;
+          }
     }
     MapCache16& c = map_cache16();
     std::lock_guard<std::mutex> g(c.mu);
@@ -557,3 +665,9 @@ int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coor
 }
 
 }  // namespace raftcorr
+
+#ifdef RAFTCORR_L16_TRACE
+extern "C" int raftcorr_debug_l16_trace(unsigned long long* host, int count) {
+  return (int)cudaMemcpyFromSymbol(host, raftcorr::g_trace16, sizeof(unsigned long long) * count);
+}
+#endif

@@ -32,7 +32,8 @@ LevelArray = Level * MAX_LEVELS
 class Level16(ctypes.Structure):
     """struct raftcorr_level16: bfloat16 pixels in 4x8 blocks of 64 bytes"""
     _fields_ = [("data", ctypes.c_void_p), ("H", ctypes.c_int32), ("W", ctypes.c_int32),
-                ("blocks_x", ctypes.c_int32), ("blocks_y", ctypes.c_int32), ("image_stride", ctypes.c_int64)]
+                ("blocks_x", ctypes.c_int32), ("blocks_y", ctypes.c_int32),
+                ("interleave_log2", ctypes.c_int32), ("reserved", ctypes.c_int32), ("image_stride", ctypes.c_int64)]
 
 
 Level16Array = Level16 * MAX_LEVELS

@@ -93,43 +93,59 @@ class Pyramid:
 
 class Pyramid16:
     """Device storage of a correlation pyramid in 16 bits (include/raftcorr.h, raftcorr_level16): bfloat16
-    pixels in blocks of 4 rows x 8 columns, ``storage[l]`` indexed [image][block row][block col][row][col].
+    pixels in blocks of 4 rows x 8 columns, ``storage[l]`` indexed
+    [group of G images][block row][block col][image in group][row][col] with G = 2**interleave_log2 (1 = plain).
     Half the bytes of ``Pyramid`` for the build to write and the lookup to read; inference only."""
 
-    def __init__(self, B: int, H: int, W: int, num_levels: int, device, zero: bool = False):
+    def __init__(self, B: int, H: int, W: int, num_levels: int, device, zero: bool = False, interleave=None):
+        """interleave: None = the library's choice (raftcorr_pyramid16_layout), False = plain blocked levels,
+        or interleave_log2 per level."""
         self.B, self.H, self.W, self.num_levels = B, H, W, num_levels
         self.desc = Level16Array()
         nbytes = (ctypes.c_int64 * _capi.MAX_LEVELS)()
         _capi.check(_capi.lib().raftcorr_pyramid16_layout(B, H, W, num_levels, self.desc, nbytes),
                     "raftcorr_pyramid16_layout")
+        if interleave is False:
+            interleave = (0,) * num_levels
+        if interleave is not None:                      # explicit log2 per level (tests, measurements)
+            for l in range(num_levels):
+                self.desc[l].interleave_log2 = int(interleave[l])
         alloc = torch.zeros if zero else torch.empty
         self.storage: List[torch.Tensor] = []
         for l in range(num_levels):
             d = self.desc[l]
-            buf = alloc((B * H * W, d.blocks_y, d.blocks_x, 4, 8), dtype=torch.bfloat16, device=device)
+            g = 1 << d.interleave_log2
+            assert (B * H * W) % g == 0
+            buf = alloc((B * H * W // g, d.blocks_y, d.blocks_x, g, 4, 8), dtype=torch.bfloat16, device=device)
             d.data = buf.data_ptr()
             self.storage.append(buf)
 
+    def padded(self, l: int) -> torch.Tensor:
+        """Level l de-blocked, padding pixels included: (B*H*W, 4*blocks_y, 8*blocks_x) bfloat16 (a copy)."""
+        d, s = self.desc[l], self.storage[l]                    # [group][by][bx][g][4][8]
+        return s.permute(0, 3, 1, 4, 2, 5).reshape(s.shape[0] * s.shape[3], 4 * d.blocks_y, 8 * d.blocks_x)
+
     def dense(self, l: int) -> torch.Tensor:
         """Level l de-blocked and widened: (B*H*W, H_l, W_l) float32 (a copy; layout conversion only)."""
-        d, s = self.desc[l], self.storage[l]
-        full = s.permute(0, 1, 3, 2, 4).reshape(s.shape[0], 4 * d.blocks_y, 8 * d.blocks_x)
-        return full[:, : d.H, : d.W].float()
+        d = self.desc[l]
+        return self.padded(l)[:, : d.H, : d.W].float()
 
     def views(self) -> List[torch.Tensor]:
         """(B*H*W, 1, H_l, W_l) float32 tensors, the shape core/corr.py:22-27 exposes (copies)."""
         return [self.dense(l).unsqueeze(1) for l in range(self.num_levels)]
 
     @classmethod
-    def from_dense(cls, levels: Sequence[torch.Tensor], B: int, H: int, W: int, device="cuda") -> "Pyramid16":
+    def from_dense(cls, levels: Sequence[torch.Tensor], B: int, H: int, W: int, device="cuda",
+                   interleave=None) -> "Pyramid16":
         """Blocked bf16 copy of reference-shaped levels (B*H*W, 1, H_l, W_l) (rounded to bf16, padding zeroed)."""
-        pyr = cls(B, H, W, len(levels), device, zero=True)
+        pyr = cls(B, H, W, len(levels), device, zero=True, interleave=interleave)
         for l, lv in enumerate(levels):
             d = pyr.desc[l]
             t = torch.as_tensor(lv, device=device).reshape(B * H * W, d.H, d.W).to(torch.bfloat16)
             full = torch.zeros((B * H * W, 4 * d.blocks_y, 8 * d.blocks_x), dtype=torch.bfloat16, device=device)
             full[:, : d.H, : d.W] = t
-            pyr.storage[l].copy_(full.reshape(B * H * W, d.blocks_y, 4, d.blocks_x, 8).permute(0, 1, 3, 2, 4))
+            g = 1 << d.interleave_log2
+            pyr.storage[l].copy_(full.reshape(B * H * W // g, g, d.blocks_y, 4, d.blocks_x, 8).permute(0, 2, 4, 1, 3, 5))
         return pyr
 
 
@@ -149,7 +165,7 @@ def resolve_storage(storage, precision: int, D: int, num_levels: int, radius) ->
 
 
 def build_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
-                  precision=None, storage="fp32", radius=None):
+                  precision=None, storage="fp32", radius=None, interleave=None):
     """core/corr.py:13-27 + 52-60 in one launch sequence (pack, tcgen05 GEMM + pooled epilogue).
     Returns a ``Pyramid`` (fp32 rows) or, for storage 'bf16' / 'auto', a ``Pyramid16`` (blocked bfloat16)."""
     _require_cuda_f32(fmap1, "fmap1")
@@ -162,7 +178,7 @@ def build_pyramid(fmap1: torch.Tensor, fmap2: torch.Tensor, num_levels: int = 4,
     lib = _capi.lib()
     if resolve_storage(storage, prec, D, num_levels, radius) == "bf16":
         with torch.cuda.device(fmap1.device):
-            pyr16 = Pyramid16(B, H, W, num_levels, fmap1.device)
+            pyr16 = Pyramid16(B, H, W, num_levels, fmap1.device, interleave=interleave)
             ws_bytes = int(lib.raftcorr_build_workspace_bytes(B, D, H, W, PREC_BF16))
             ws = torch.empty(max(ws_bytes, 1), dtype=torch.uint8, device=fmap1.device)
             _capi.check(lib.raftcorr_build_pyramid16(fmap1.data_ptr(), fmap2.data_ptr(), B, D, H, W, num_levels,

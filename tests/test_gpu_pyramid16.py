@@ -29,44 +29,51 @@ def _levels_numpy(pyr16):
 
 def _padding_is_zero(pyr16):
     for l in range(pyr16.num_levels):
-        d, s = pyr16.desc[l], pyr16.storage[l]
-        full = s.permute(0, 1, 3, 2, 4).reshape(s.shape[0], 4 * d.blocks_y, 8 * d.blocks_x)
-        bits = full.view(torch.int16)
+        d = pyr16.desc[l]
+        bits = pyr16.padded(l).contiguous().view(torch.int16)
         if bits[:, d.H:, :].ne(0).any() or bits[:, :, d.W:].ne(0).any():
             return False
     return True
 
 
-def test_layout_matches_the_header_formula():
-    """pixel (y, x) of image n at byte n*image_stride + ((y>>2)*blocks_x + (x>>3))*64 + (y&3)*16 + (x&7)*2."""
-    B, H, W = 1, 9, 21
+@pytest.mark.parametrize("size,interleave", [((1, 9, 21), None), ((2, 8, 22), None), ((2, 8, 22), False)])
+def test_layout_matches_the_header_formula(size, interleave):
+    """pixel (y, x) of image n at byte (n // G) * G * image_stride + (((y>>2)*blocks_x + (x>>3)) * G + n % G) * 64
+    + (y&3)*16 + (x&7)*2, G = 2**interleave_log2 (include/raftcorr.h)."""
+    B, H, W = size
     gen = torch.Generator().manual_seed(1)
     levels = [torch.randn(B * H * W, 1, max(H >> l, 1), max(W >> l, 1), generator=gen) for l in range(3)]
-    pyr = ops.Pyramid16.from_dense(levels, B, H, W)
+    pyr = ops.Pyramid16.from_dense(levels, B, H, W, interleave=interleave)
+    want_g = [2, 2, 0] if (H * W) % 4 == 0 and interleave is None else [0, 0, 0]
     for l in range(3):
         d = pyr.desc[l]
         assert (d.blocks_x, d.blocks_y, d.image_stride) == ((d.W + 7) // 8, (d.H + 3) // 4, ((d.W + 7) // 8) * ((d.H + 3) // 4) * 64)
+        assert d.interleave_log2 == want_g[l]
+        G = 1 << d.interleave_log2
         raw = pyr.storage[l].reshape(-1).view(torch.int16).cpu()
         want = levels[l].to(torch.bfloat16).view(torch.int16)
-        for (n, y, x) in [(0, 0, 0), (5, d.H - 1, d.W - 1), (B * H * W - 1, d.H // 2, d.W // 3)]:
-            byte = n * d.image_stride + ((y >> 2) * d.blocks_x + (x >> 3)) * 64 + (y & 3) * 16 + (x & 7) * 2
+        for (n, y, x) in [(0, 0, 0), (5, d.H - 1, d.W - 1), (B * H * W - 1, d.H // 2, d.W // 3), (6, 0, d.W - 1)]:
+            byte = (n // G) * G * d.image_stride + (((y >> 2) * d.blocks_x + (x >> 3)) * G + n % G) * 64 + (y & 3) * 16 + (x & 7) * 2
             assert raw[byte // 2].item() == want[n, 0, y, x].item(), (l, n, y, x)
         assert torch.equal(pyr.dense(l).cpu(), levels[l][:, 0].to(torch.bfloat16).float())
     assert _padding_is_zero(pyr)
 
 
 SHAPES = [(1, 64, 16, 18), (2, 32, 17, 23), (1, 128, 46, 62), (1, 8, 55, 96), (2, 16, 24, 40), (1, 24, 9, 33),
-          (1, 16, 8, 8), (1, 40, 33, 65)]
+          (1, 16, 8, 8), (1, 40, 33, 65),
+          (2, 32, 10, 10), (3, 16, 12, 14)]   # H*W % 4 == 0 but % 32 != 0: interleaved levels, tiles that end mid-warp
 
 
+@pytest.mark.parametrize("interleave", [None, False])
 @pytest.mark.parametrize("shape", SHAPES)
-def test_build16_against_oracle_and_fp32_pyramid(shape):
+def test_build16_against_oracle_and_fp32_pyramid(shape, interleave):
     B, D, H, W = shape
     gen = torch.Generator().manual_seed(B * 1000 + H * W)
     f1 = torch.randn(B, D, H, W, generator=gen)
     f2 = torch.randn(B, D, H, W, generator=gen)
-    pyr16 = ops.build_pyramid(f1.cuda(), f2.cuda(), 4, "bf16", storage="bf16")
+    pyr16 = ops.build_pyramid(f1.cuda(), f2.cuda(), 4, "bf16", storage="bf16", interleave=interleave)
     assert isinstance(pyr16, ops.Pyramid16)
+    assert pyr16.desc[0].interleave_log2 == (2 if interleave is None and (H * W) % 4 == 0 else 0)
     want = oracle.build_pyramid(f1, f2, 4)
     wide = ops.build_pyramid(f1.cuda(), f2.cuda(), 4, "bf16", storage="fp32")
     for l in range(4):
@@ -102,11 +109,12 @@ def test_build16_overwrites_stale_padding():
 @pytest.mark.parametrize("kind", KINDS)
 @pytest.mark.parametrize("case", [(1, 16, 18, 4), (2, 17, 23, 3), (1, 46, 62, 4), (3, 9, 33, 4), (1, 16, 95, 3), (1, 16, 16, 4),
                                   (6, 40, 70, 4)])   # the last one: several tiles per CTA, the rings wrap
-def test_lookup16_bit_exact_against_oracle(case, kind):
+@pytest.mark.parametrize("interleave", [None, False])
+def test_lookup16_bit_exact_against_oracle(case, kind, interleave):
     B, H, W, r = case
     gen = torch.Generator().manual_seed(H * 100 + W + r)
     levels = [torch.randn(B * H * W, 1, H >> l, W >> l, generator=gen) for l in range(4)]
-    pyr = ops.Pyramid16.from_dense(levels, B, H, W)
+    pyr = ops.Pyramid16.from_dense(levels, B, H, W, interleave=interleave)
     stored = _levels_numpy(pyr)                     # what the kernel reads: bf16 values, widened
     c = coords_for(kind, B, H, W, gen)
     out = ops.lookup(pyr, c.cuda(), r, "aten_cpu").cpu().numpy()

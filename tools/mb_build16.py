@@ -4,11 +4,12 @@ from raftcorr_b200 import ops
 B, D, H, W = 8, 256, 55, 128
 torch.manual_seed(0)
 fs = [(torch.randn(B, D, H, W, device="cuda"), torch.randn(B, D, H, W, device="cuda")) for _ in range(2)]
-for i in range(3): ops.build_pyramid(*fs[i & 1], 4, "bf16", storage="bf16")
-ts = []
-for i in range(10):
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record(); p = ops.build_pyramid(*fs[i & 1], 4, "bf16", storage="bf16"); b.record(); torch.cuda.synchronize(); ts.append(a.elapsed_time(b)); del p
-ts.sort()
 fl = 2.0 * B * (H * W) ** 2 * D
-print(f"RAFTCORR_B16_DEBUG={os.environ.get('RAFTCORR_B16_DEBUG','0')}: build16 (pack + gemm) {ts[5]*1e3:.1f} us  {fl/ts[5]/1e9:.0f} TFLOP/s", flush=True)
+for il in (None, False, (2, 0, 0, 0), (0, 2, 0, 0), (2, 2, 0, 0)):
+    for i in range(3): ops.build_pyramid(*fs[i & 1], 4, "bf16", storage="bf16", interleave=il)
+    ts = []
+    for i in range(10):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); p = ops.build_pyramid(*fs[i & 1], 4, "bf16", storage="bf16", interleave=il); b.record(); torch.cuda.synchronize(); ts.append(a.elapsed_time(b)); del p
+    ts.sort()
+    print(f"interleave={il}: build16 (pack + gemm) {ts[5]*1e3:.1f} us  {fl/ts[5]/1e9:.0f} TFLOP/s", flush=True)
