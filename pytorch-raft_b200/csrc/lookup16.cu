@@ -117,7 +117,9 @@ __device__ __forceinline__ int slot_of(int lane, int level) {
   return lane;
 }
 // physical shared-memory address of logical byte `a` of a box fetched with CU_TENSOR_MAP_SWIZZLE_64B
-__device__ __forceinline__ uint32_t swz64(uint32_t a) { return a ^ ((a >> 3) & 0x30u); }
+// (mask 0x30); a group's box out of an interleaved level has 128-byte rows (the blocks of two neighbouring images) and
+// is fetched with the 128-byte swizzle (chunk bits 4-6 ^= address bits 7-9, mask 0x70): eight phases for eight groups
+__device__ __forceinline__ uint32_t swz(uint32_t a, uint32_t mask) { return a ^ ((a >> 3) & mask); }
 
 // window of one query at one level, shared by producer and sampler (same code, same result)
 struct Window {
@@ -196,14 +198,14 @@ __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img
 // the variants of this routine came to 10k SASS instructions and the warps of an SM — each in a different variant
 // or phase — spent 40 % of their issue slots waiting for the instruction cache.
 template <int R, int kMode, bool kFlips, bool kAllLive>
-__device__ __forceinline__ void sample_unit(uint32_t slot_addr, int cshift, int bw, int bh, int bx0, int by0, int mx, int my,
+__device__ __forceinline__ void sample_unit(uint32_t slot_addr, uint32_t swz_mask, int cshift, int bw, int bh, int bx0, int by0, int mx, int my,
                                             float cxl, const Level16Dev& lv, const Tap (&ty)[2 * R + 1], int i_begin,
                                             int i_end, float* optr, long long N, bool live) {
   constexpr int rd = 2 * R + 1, kRows = rd + 1 + (kFlips ? 1 : 0);
   const int rowpitch = bw << cshift;   // bytes per block row of the box (a block column is 1 << cshift bytes wide)
   auto px = [&](uint32_t row, uint32_t col) -> float {
     unsigned short v;
-    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz64(row + col)));
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz(row + col, swz_mask)));
     return bf16_bits_to_float(v);
   };
   auto combine = [&](float vnw, float vne, float vsw, float vse, float w_, float e_, float n_, float s_) {
@@ -285,6 +287,98 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, int cshift, int 
       c0[r] = c1[r];
       if (kFlips) c1[r] = c2[r];
     }
+  }
+}
+
+// The dense footprint again (kFlips = false), two outputs per floating-point instruction: sm_100's packed fp32
+// operations (fma.rn.f32x2 & co.: each half is the IEEE operation, so the bits do not change) halve the issue slots
+// of the weight products and the four-term sum, which are 45 % of this routine.  Outputs j and j + 2 of an x tap
+// share an instruction: their upper-left pixels are patch rows (j, j + 2) and their lower-left ones (j + 1, j + 3),
+// which is also the upper-left pair of outputs (j + 1, j + 3) — only rows 2, 4, 6 are needed in two pairs.
+#ifndef RAFTCORR_L16_PAIRED
+#define RAFTCORR_L16_PAIRED 1
+#endif
+template <int R, int kMode, bool kAllLive>
+__device__ __forceinline__ void sample_unit_dense2(uint32_t slot_addr, uint32_t swz_mask, int cshift, int bw, int bx0, int by0, int mx, int my,
+                                                   float cxl, const Level16Dev& lv, const Tap (&ty)[2 * R + 1],
+                                                   int i_begin, int i_end, float* optr, unsigned N, bool live) {
+  constexpr int rd = 2 * R + 1, kRows = rd + 1;
+  constexpr int kPairs = (rd - 1) / 2;                    // rd = 9: (0,2) (1,3) (4,6) (5,7) + 8;  rd = 7: (0,2) (1,3) (4,6) + 5
+  constexpr int kSingle = rd == 9 ? 8 : 5;
+  static_assert(rd == 9 || rd == 7, "pairing tables cover radius 3 and 4");
+  auto lo_of = [](int p) { return 4 * (p >> 1) + (p & 1); };
+  const int rowpitch = bw << cshift;
+  auto px = [&](uint32_t row, uint32_t col) -> float {
+    unsigned short v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(swz(row + col, swz_mask)));
+    return bf16_bits_to_float(v);
+  };
+  uint32_t rows[kRows];
+#pragma unroll
+  for (int r = 0; r < kRows; ++r) {
+    const int yy = my + r - 4 * by0;
+    rows[r] = slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16);
+  }
+  auto col_off = [&](int c) {
+    const int xx = mx + c - 8 * bx0;
+    return (uint32_t)(((xx >> 3) << cshift) + (xx & 7) * 2);
+  };
+  float2 wn[kPairs], ws[kPairs];   // (fy_j, fy_j+2) and (1 - fy_j, 1 - fy_j+2)
+#pragma unroll
+  for (int p = 0; p < kPairs; ++p) {
+    const int lo = lo_of(p);
+    wn[p] = make_float2(ty[lo].frac, ty[lo + 2].frac);
+    ws[p] = make_float2(__fsub_rn(1.0f, ty[lo].frac), __fsub_rn(1.0f, ty[lo + 2].frac));
+  }
+  const float n1 = ty[kSingle].frac, s1 = __fsub_rn(1.0f, n1);
+  struct Col {
+    float2 tl[kPairs], bl[kPairs];
+    float t1, b1;
+  };
+  auto load_col = [&](uint32_t coff) {
+    float v[kRows];
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) v[r] = px(rows[r], coff);
+    Col c;
+#pragma unroll
+    for (int p = 0; p < kPairs; ++p) {
+      const int lo = lo_of(p);
+      c.tl[p] = make_float2(v[lo], v[lo + 2]);
+      c.bl[p] = make_float2(v[lo + 1], v[lo + 3]);
+    }
+    c.t1 = v[kSingle];
+    c.b1 = v[kSingle + 1];
+    return c;
+  };
+  Col L = load_col(col_off(i_begin));
+#pragma unroll kUnroll16
+  for (int i = i_begin; i < i_end; ++i) {
+    const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
+    const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
+    const float2 e2 = make_float2(ex, ex), w2 = make_float2(fx, fx);
+    const Col Rt = load_col(col_off(i + 1));
+    float* o = optr + (size_t)(unsigned)(i * rd) * N;
+#pragma unroll
+    for (int p = 0; p < kPairs; ++p) {
+      const int lo = lo_of(p);
+      // ATen's order (common.cuh bilinear_combine): nw = s*e, ne = s*w, sw = n*e, se = n*w; ((nw.v + ne.v) + sw.v) + se.v by fma
+      float2 acc = __fmul2_rn(L.tl[p], __fmul2_rn(ws[p], e2));
+      acc = __ffma2_rn(Rt.tl[p], __fmul2_rn(ws[p], w2), acc);
+      acc = __ffma2_rn(L.bl[p], __fmul2_rn(wn[p], e2), acc);
+      acc = __ffma2_rn(Rt.bl[p], __fmul2_rn(wn[p], w2), acc);
+      if (kAllLive || live) {
+        __stcs(o + (size_t)N * (unsigned)lo, acc.x);
+        __stcs(o + (size_t)N * (unsigned)(lo + 2), acc.y);
+      }
+    }
+    {
+      float acc = __fmul_rn(L.t1, __fmul_rn(s1, ex));
+      acc = __fmaf_rn(Rt.t1, __fmul_rn(s1, fx), acc);
+      acc = __fmaf_rn(L.b1, __fmul_rn(n1, ex), acc);
+      acc = __fmaf_rn(Rt.b1, __fmul_rn(n1, fx), acc);
+      if (kAllLive || live) __stcs(o + (size_t)N * (unsigned)kSingle, acc);
+    }
+    L = Rt;
   }
 }
 
@@ -464,6 +558,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     const int bw = 2 + w.wide, bh = 3 + w.tall;
     const uint32_t slot_addr = slot_of_window(w);
     const int cshift = 6 + (w.grouped ? ilog : 0);
+    const uint32_t swz_mask = (w.grouped && ilog) ? 0x70u : 0x30u;
     // floor flips: is tap j on pixel m + j + e_j with e_j in {0,1}?
     int mx = tx[0].i0, my = ty[0].i0, hx = tx[0].i0, hy = ty[0].i0;
 #pragma unroll
@@ -489,12 +584,19 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
       // a window that does not fit a box (|coords| beyond ~2^20) or an irregular tap pattern somewhere in the warp:
       // every lane samples straight from global memory
       if (live) sample_unit_global<R, kMode>(lv, cur.img, cur.cxl, cur.cyl, ib, ie, cur.optr, N);
+#if RAFTCORR_L16_PAIRED
     } else if (all_chain && all_live) {
-      sample_unit<R, kMode, false, true>(slot_addr, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+      sample_unit_dense2<R, kMode, true>(slot_addr, swz_mask, cshift, bw, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, (unsigned)N, live);
     } else if (all_chain) {
-      sample_unit<R, kMode, false, false>(slot_addr, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+      sample_unit_dense2<R, kMode, false>(slot_addr, swz_mask, cshift, bw, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, (unsigned)N, live);
+#else
+    } else if (all_chain && all_live) {
+      sample_unit<R, kMode, false, true>(slot_addr, swz_mask, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+    } else if (all_chain) {
+      sample_unit<R, kMode, false, false>(slot_addr, swz_mask, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+#endif
     } else {
-      sample_unit<R, kMode, true, false>(slot_addr, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+      sample_unit<R, kMode, true, false>(slot_addr, swz_mask, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
     }
     L16_TICK(t3);
     if (more) {
@@ -625,8 +727,18 @@ int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coor
       for (int grouped = 0; grouped < 2; ++grouped)
         for (int wide = 0; wide < 2; ++wide)
           for (int tall = 0; tall < 2; ++tall) {
+            if (grouped && ilog) {
+              // the blocks of two neighbouring images as one 128-byte row: (row, image pair, block column, block row, group)
+              cuuint64_t d2[5] = {64, members / 2, dims[2], dims[3], dims[4]};
+              cuuint64_t s2[4] = {128, strides[1], strides[2], strides[3]};
+              cuuint32_t b2[5] = {64, (cuuint32_t)(G / 2), (cuuint32_t)(2 + wide), (cuuint32_t)(3 + tall), 1};
+              if (int rc = encode(&maps.m[l][grouped][wide][tall], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, levels[l].data, d2, s2,
+                                  b2, CU_TENSOR_MAP_SWIZZLE_128B, "lookup16 group window", CU_TENSOR_MAP_L2_PROMOTION_NONE))
+                return rc;
+              continue;
+            }
             cuuint32_t box[5] = {32, 1, (cuuint32_t)(2 + wide), (cuuint32_t)(3 + tall), 1};
-            if (grouped) box[ilog ? 1 : 4] = (cuuint32_t)G;
+            if (grouped) box[4] = (cuuint32_t)G;
             if (box[4] > dims[4]) box[4] = (cuuint32_t)dims[4];   // (never used then: a group needs 2^g live queries)
             if (int rc = encode(&maps.m[l][grouped][wide][tall], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, levels[l].data, dims,
                                 strides, box, CU_TENSOR_MAP_SWIZZLE_64B, "lookup16 window", CU_TENSOR_MAP_L2_PROMOTION_NONE))
