@@ -9,26 +9,37 @@
 //
 //   unit      = 32 consecutive-x queries of one fmap row at ONE pyramid level (4 units per tile)
 //   warp      = owns one unit buffer and walks every other tile of its level (8 warps: 4 levels x 2).  Lane q
-//               derives its query's window and the warp requests one TMA box per lane (cp.async.bulk.tensor.4d over
-//               the level's (64-byte block, blocks_x, blocks_y, image) tensor: {2,3} x {3,4} whole blocks;
-//               out-of-image blocks arrive as zeros = grid_sample's zero padding) into the lane's slot, all 32
-//               boxes on one mbarrier.  When they have landed, lane q forms its query's (2r+1)^2 samples out of
-//               its own slot and stores them straight to the NCHW output — for a fixed channel the 32 lanes are
-//               32 consecutive x, so every store instruction is one full 128-byte line and the output never
-//               passes through shared memory.  Then the warp refills its buffer with its next unit; the other
-//               seven warps keep the SM busy meanwhile.
-//               (Measured alternatives, all slower at BASELINE.json configs[1]: dedicated producer warps — one
-//               warp issues a box only every ~140 cycles; two warps per unit splitting the x taps — the per-unit
-//               work (tap tables, window, issue) is then paid twice; staging the patch in registers to refill
-//               early; L2 prefetch of the next unit.  RAFTCORR_L16_SPLIT=2 builds the two-warp variant.)
+//               derives its query's window ({2,3} x {3,4} whole 64-byte blocks; out-of-image blocks arrive as
+//               zeros = grid_sample's zero padding).  Neighbouring queries look at nearly the same place of
+//               neighbouring images, so the four lanes of a group take the union of their windows and the
+//               group's first lane requests ONE box over the four images (cp.async.bulk.tensor.5d); a group
+//               whose union does not fit a box shape (flow discontinuity, image border of the batch) falls back
+//               to one box per lane.  All boxes of a unit arrive on one mbarrier.  Then lane q forms its
+//               query's (2r+1)^2 samples out of its part of the buffer and stores them straight to the NCHW
+//               output — for a fixed channel the 32 lanes are 32 consecutive x, so every store instruction is
+//               one full 128-byte line and the output never passes through shared memory.  Then the warp refills
+//               its buffer with its next unit; the other seven warps keep the SM busy meanwhile.
+//   levels    = plain ([image][block row][block][64 B]) or interleaved ([group of 4 images][block row][block]
+//               [image][64 B], raftcorr_level16.interleave_log2): with the latter a group's box reads pieces of
+//               512-768 contiguous bytes instead of four pieces of 128-192 bytes 14 KB apart.  Measured with
+//               tools/probe/tma_latency_probe.cu: the scattered form tops out at 3.4 TB/s and, at this kernel's
+//               load, makes a warp wait ~5100 cycles for its unit; interleaved 4.8 TB/s and ~2400 cycles.
 //
-// Shared memory: 8 unit buffers x 32 slots x 896 B.  The 32 windows are walked in lock step, at the same
-// in-window offset more often than not, and TMA wants 128-byte aligned destinations, so unskewed slots would put
-// all lanes on one bank.  The boxes are therefore fetched with the 64-byte TMA swizzle (16-byte chunk index
-// bits 4-5 ^= address bits 7-8; measured layout: tools/probe/tma_swizzle_probe.cu — the 128-byte swizzle pads
-// every 64-byte block to a 128-byte row and would double the footprint) at a slot pitch that is an odd multiple
-// of 128 B: four skew classes.  The slot order puts lanes whose windows start one pixel apart at their level
-// into the same class, so that class mates fall on different words.
+// Where the time goes (tools/trace16.py, cycles per unit and warp at BASELINE.json configs[1], smooth flow):
+// prepare (taps, windows of this and the next unit) ~1600, wait for the boxes ~1750, sample ~3800, issue ~950; a
+// warp issues a box only every ~70-110 cycles whatever the box holds (operands travel through uniform registers
+// one elected lane at a time), which is why boxes are shared by groups.  Measured alternatives, all slower:
+// dedicated producer warps; two warps per unit splitting the x taps (the per-unit work is paid twice: 35.7 us
+// against 33.1); staging the patch in registers to refill early; L2 prefetch of the next unit (a prefetch costs
+// the same issue time as the load); 12 warps with packed 18.5 KB buffers; groups of 2 or 8 (same time as 4).
+//
+// Shared memory: 8 unit buffers of 28 KB.  The 32 windows are walked in lock step, at the same in-window offset
+// more often than not, and TMA wants 128-byte aligned destinations, so without a skew all lanes would hit one
+// bank.  Boxes are therefore fetched with a TMA swizzle (64-byte swizzle: 16-byte chunk index bits 4-5 ^= address
+// bits 7-8; measured layout: tools/probe/tma_swizzle_probe.cu — with 64-byte rows the 128-byte swizzle would pad
+// every block to 128 bytes; interleaved group boxes have 128-byte rows and use the 128-byte swizzle, bits 4-6 ^=
+// bits 7-9) into regions whose pitch is an odd multiple of 128 B, so that neighbouring groups start in
+// different swizzle phases.
 #include <stdlib.h>
 #include <string.h>
 
@@ -45,15 +56,11 @@ namespace {
 using namespace lk;
 
 constexpr int kL = RAFTCORR_MAX_LEVELS;           // the kernel is specialised for the 4-level pyramid
-#ifndef RAFTCORR_L16_SPLIT
-#define RAFTCORR_L16_SPLIT 1
-#endif
 #ifndef RAFTCORR_L16_UNROLL
 #define RAFTCORR_L16_UNROLL 2
 #endif
 constexpr int kUnroll16 = RAFTCORR_L16_UNROLL;     // unroll factor of the x-tap loop
-constexpr int kSplit16 = RAFTCORR_L16_SPLIT;       // warps per unit buffer (they split the x taps)
-constexpr int kWarps16 = 8 * kSplit16;             // per level: 2 unit buffers x kSplit16 warps
+constexpr int kWarps16 = 8;                        // per level: 2 warps, each with its own unit buffer
 constexpr int kThreads16 = kWarps16 * 32;
 constexpr int kDepth16 = 2;                        // unit buffers per level (each level runs its own ring)
 constexpr int kBufs = kL * kDepth16;
@@ -295,9 +302,6 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, uint32_t swz_mas
 // of the weight products and the four-term sum, which are 45 % of this routine.  Outputs j and j + 2 of an x tap
 // share an instruction: their upper-left pixels are patch rows (j, j + 2) and their lower-left ones (j + 1, j + 3),
 // which is also the upper-left pair of outputs (j + 1, j + 3) — only rows 2, 4, 6 are needed in two pairs.
-#ifndef RAFTCORR_L16_PAIRED
-#define RAFTCORR_L16_PAIRED 1
-#endif
 template <int R, int kMode, bool kAllLive>
 __device__ __forceinline__ void sample_unit_dense2(uint32_t slot_addr, uint32_t swz_mask, int cshift, int bw, int bx0, int by0, int mx, int my,
                                                    float cxl, const Level16Dev& lv, const Tap (&ty)[2 * R + 1],
@@ -404,14 +408,13 @@ __global__ void __launch_bounds__(kThreads16, 1)
 lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant__ Lookup16Maps maps) {
   constexpr int rd = 2 * R + 1, rd2 = rd * rd;
   constexpr int kChannels = kL * rd2;
-  constexpr int kMid = (rd + 1) / 2;     // a pair splits the x taps: [0, kMid) and [kMid, rd)
   extern __shared__ __align__(1024) unsigned char smem[];
   const uint32_t smem_base = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   auto full_bar = [&](int b) { return smem_base + kOffBars16 + b * 8; };
 
   if (threadIdx.x < kBufs) {
-    mbar_init(full_bar(threadIdx.x), kSplit16);   // one arrive.expect_tx per warp of the pair (+ the bytes of its boxes)
+    mbar_init(full_bar(threadIdx.x), 1);   // one arrive.expect_tx per refill (+ the bytes of its boxes)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -419,8 +422,8 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
   const long long N = (long long)p.H * p.W;
   const int n_tiles = (int)((p.tiles - blockIdx.x + gridDim.x - 1) / gridDim.x);   // tiles of this CTA
 
-  // warp pair = one unit buffer: pairs 2l, 2l+1 belong to level l and take alternate tiles
-  const int pair = warp / kSplit16, h = warp % kSplit16;
+  // one warp = one unit buffer: warps 2l, 2l+1 belong to level l and take alternate tiles
+  const int pair = warp;
   const int level = pair >> 1, first = pair & 1;
   const Level16Dev lv = p.lv[level];
   const int glog = group_log2(level), gl = lane & ((1 << glog) - 1);
@@ -500,10 +503,10 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
       cy = __ldg(ptr + N);
     }
   };
-  // this warp requests the boxes of lanes 16h .. 16h+15 of the pair's next unit
+  // request the boxes of a unit: one per group, or one per lane where the group has no common box
   auto issue = [&](const Unit& u, const Window& w) {
     const int bw = 2 + w.wide, bh = 3 + w.tall;
-    uint32_t bytes = (u.live && w.fast && (kSplit16 == 1 || (lane >> 4) == h)) ? (uint32_t)(bw * bh * 64) : 0u;
+    uint32_t bytes = (u.live && w.fast) ? (uint32_t)(bw * bh * 64) : 0u;
     if (w.grouped) bytes = gl == 0 ? bytes << glog : 0u;   // the group's first lane fetches for all of them
     const uint32_t total = __reduce_add_sync(0xffffffffu, bytes);
     if (lane == 0) mbar_expect_tx(bar, total);
@@ -578,31 +581,23 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     L16_TICK(t2);
     phase ^= 1u;
     const bool all_flips = __all_sync(0xffffffffu, flips_ok || !live);
-    const int ib = (kSplit16 == 2 && h) ? kMid : 0, ie = (kSplit16 == 2 && !h) ? kMid : rd;
+    constexpr int ib = 0, ie = rd;
     if (p.debug & 1) {
     } else if (!all_fast || !all_flips) {
       // a window that does not fit a box (|coords| beyond ~2^20) or an irregular tap pattern somewhere in the warp:
       // every lane samples straight from global memory
       if (live) sample_unit_global<R, kMode>(lv, cur.img, cur.cxl, cur.cyl, ib, ie, cur.optr, N);
-#if RAFTCORR_L16_PAIRED
     } else if (all_chain && all_live) {
       sample_unit_dense2<R, kMode, true>(slot_addr, swz_mask, cshift, bw, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, (unsigned)N, live);
     } else if (all_chain) {
       sample_unit_dense2<R, kMode, false>(slot_addr, swz_mask, cshift, bw, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, (unsigned)N, live);
-#else
-    } else if (all_chain && all_live) {
-      sample_unit<R, kMode, false, true>(slot_addr, swz_mask, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
-    } else if (all_chain) {
-      sample_unit<R, kMode, false, false>(slot_addr, swz_mask, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
-#endif
     } else {
       sample_unit<R, kMode, true, false>(slot_addr, swz_mask, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
     }
     L16_TICK(t3);
     if (more) {
-      // both warps of the pair are done reading the buffer before either refills it
-      if (kSplit16 == 2) asm volatile("bar.sync %0, 64;" ::"r"(1 + pair) : "memory");
-      else __syncwarp();
+      // every lane is done reading the buffer before it is refilled
+      __syncwarp();
       issue(nxt, wn);
     }
     cur = nxt;
