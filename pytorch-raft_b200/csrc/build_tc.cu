@@ -142,7 +142,8 @@ __device__ __forceinline__ void stage16_chunk(uint32_t buf, int lane, int c, uin
                : "memory");
 }
 
-template <bool kTf32, bool kOut16>
+// kOut16: 0 = fp32 rows, 1 = 16-bit blocked levels, 2 = the same with levels 0 and 1 interleaved by four images
+template <bool kTf32, int kOut16>
 __global__ void __launch_bounds__(kThreads, 1)
 build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
                 const __grid_constant__ CUtensorMap mapL0, const __grid_constant__ CUtensorMap mapL1,
@@ -277,7 +278,8 @@ build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
         }
         continue;
       }
-      if constexpr (kOut16) {
+      if constexpr (kOut16 != 0) {
+        constexpr int kIlog = kOut16 == 2 ? 2 : 0;
         // bf16 pixels in 4x8 blocks.  An 8x32 tile is 2 block rows x 4 blocks at level 0, one block row x 2
         // blocks at level 1, half a block at level 2 and a quarter of a block row at level 3.
         uint32_t prev[32], l1pk[32];
@@ -326,13 +328,13 @@ build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
 #pragma unroll
                   for (int r = 0; r < 4; ++r) {
                     const uint32_t* src = (r < 2 ? prev : cur) + (r & 1) * 16 + (2 * h + bl) * 4;
-                    if (p.ilog[0]) stage16_chunk_il(buf, lane, p.ilog[0], bl, r, src[0], src[1], src[2], src[3]);
+                    if constexpr (kIlog) stage16_chunk_il(buf, lane, kIlog, bl, r, src[0], src[1], src[2], src[3]);
                     else stage16_chunk<128>(buf, lane, bl * 4 + r, src[0], src[1], src[2], src[3]);
                   }
                 fence_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                  if (p.ilog[0]) store16_il(&mapL0, &mapL0t, buf, p.ilog[0], bx, by, (long long)b * p.N + q0, p.N - q0);
+                  if constexpr (kIlog) store16_il(&mapL0, &mapL0t, buf, kIlog, bx, by, (long long)b * p.N + q0, p.N - q0);
                   else tma_store_4d(&mapL0, buf, bx * 32, by, q0, b);
                   bulk_commit();
                 }
@@ -360,13 +362,13 @@ build_tc_kernel(const __grid_constant__ TcOperandMaps ops,
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
               const uint32_t* src = l1pk + r * 8 + bl * 4;
-              if (p.ilog[1]) stage16_chunk_il(buf, lane, p.ilog[1], bl, r, src[0], src[1], src[2], src[3]);
+              if constexpr (kIlog) stage16_chunk_il(buf, lane, kIlog, bl, r, src[0], src[1], src[2], src[3]);
               else stage16_chunk<128>(buf, lane, bl * 4 + r, src[0], src[1], src[2], src[3]);
             }
           fence_async_smem();
           __syncwarp();
           if (lane == 0) {
-            if (p.ilog[1]) store16_il(&mapL1, &mapL1t, buf, p.ilog[1], 2 * tx, ty, (long long)b * p.N + q0, p.N - q0);
+            if constexpr (kIlog) store16_il(&mapL1, &mapL1t, buf, kIlog, 2 * tx, ty, (long long)b * p.N + q0, p.N - q0);
             else tma_store_4d(&mapL1, buf, 2 * tx * 32, ty, q0, b);
             bulk_commit();
           }
@@ -599,15 +601,18 @@ static int launch_tc_kernel(bool tf32, const TcOperandMaps& ops, const CUtensorM
   const long long total = (long long)p.B * p.tiles_m * p.tiles_y * p.tiles_x;
   if (total == 0) return 0;
   const int grid = (int)(total < sms ? total : sms);
-  if (out16) {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<false, true><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
+  if (out16 && p.ilog[0]) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<false, 2><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
+  } else if (out16) {
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<false, 1><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
   } else if (!tf32) {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<false, false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<false, 0><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
   } else {
-    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    build_tc_kernel<true, false><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
+    RC_CHECK_CUDA(cudaFuncSetAttribute(build_tc_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    build_tc_kernel<true, 0><<<grid, kThreads, kSmemTotal, stream>>>(ops, out_maps[0], out_maps[1], out_maps[2], out_maps[3], tail_maps[0], tail_maps[1], p);
   }
   RC_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -828,7 +833,10 @@ int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int
   p.l3_data = L > 3 ? static_cast<unsigned char*>(levels[3].data) : nullptr;
   p.l3_istride = L > 3 ? levels[3].image_stride : 0;
   p.ilog[0] = levels[0].interleave_log2;
-  p.ilog[1] = L > 1 ? levels[1].interleave_log2 : 0;
+  p.ilog[1] = L > 1 ? levels[1].interleave_log2 : p.ilog[0];
+  if (p.ilog[0] != p.ilog[1] || (p.ilog[0] != 0 && p.ilog[0] != 2))
+    return fail(RAFTCORR_E_UNSUPPORTED, "build_pyramid16: levels 0 and 1 must both be plain or both interleave 4 images (got 2^%d, 2^%d)",
+                p.ilog[0], p.ilog[1]);
   return launch_tc_kernel(false, ops, mapL, p, stream, true, mapT);
 }
 
