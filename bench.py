@@ -101,6 +101,22 @@ def ncu_traffic_per_launch(kernel_key: str):
         return None
 
 
+def measure_write_only_gbs(dev, gib: int = 2, reps: int = 6):
+    """What this GPU's HBM takes when a kernel only writes (the build's situation: 1.0 GB of pyramid out, 58 MB of
+    operands in): a 2 GiB memset, best of `reps`.  MEASURED_PEAKS.json's hbm_gbs is a copy (half reads)."""
+    buf = torch.empty(gib << 30, dtype=torch.uint8, device=dev)
+    buf.zero_()
+    best = 1e9
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        buf.zero_()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return (gib << 30) / (best * 1e-3) / 1e9
+
+
 def measure_tf32_peak(dev, seconds: float = 1.5):
     """Dense TF32 peak on this GPU, measured the way MEASURED_PEAKS.json measures bf16: torch.matmul 8192^3 with
     allow_tf32 (cuBLAS), best of 10 (burst) and back to back for `seconds` (sustained).  SURVEY.md 8(d)."""
@@ -680,6 +696,7 @@ def main():
     torch.cuda.synchronize()
     build_ms = b0.elapsed_time(b1) / 6
     del fms
+    write_only_gbs = measure_write_only_gbs(dev)
 
     if rank != 0:
         if distributed:
@@ -718,7 +735,9 @@ def main():
                    "peak_burst": tf_burst, "frac_burst": build_tflops / tf_burst,
                    "which": "bf16 dense, cuBLAS 8192^3 (MEASURED_PEAKS.json)" if peaks_all else "fallback"},
         "hbm": {"achieved_gbs": build_gbs, "peak": peak, "frac": build_gbs / peak},
-        "bound": "tensor" if build_tflops / tf_sust >= build_gbs / peak else "hbm-write",
+        "hbm_write_only": {"peak": write_only_gbs, "frac": build_gbs / write_only_gbs,
+                           "how": "2 GiB torch memset on this GPU, best of 6: the roof of a kernel that only writes"},
+        "bound": "tensor" if build_tflops / tf_sust >= build_gbs / write_only_gbs else "hbm-write",
     }
     h2d = 2 * BATCH_PER_GPU * 3 * IMG_H * IMG_W * 4
     d2h = BATCH_PER_GPU * 2 * IMG_H * IMG_W * 4
