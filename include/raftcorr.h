@@ -183,6 +183,14 @@ int raftcorr_alt_fused_fwd(const void* fmap1_bf16, const void* const* fmap2_bf16
                            float* out, int B, int H1, int W1, int C, int num_levels, int radius,
                            int coord_mode, float scale, void* stream);
 
+/* The operands of raftcorr_alt_fused_fwd in one pass: replaces the avg_pool2d chain of AlternateCorrBlock.__init__
+ * (core/corr.py:64-72) and the per-call NHWC copies of core/corr.py:82-83.
+ *      fmap: (B,D,H,W) fp32 NCHW contiguous; out_levels[l], l < num_levels: (B, H>>l, W>>l, D) NHWC bfloat16, level
+ *      l+1 = the 2x2 mean of level l in fp32 (ATen's avg_pool2d arithmetic, floor on odd sizes), each value rounded
+ *      to bfloat16 once.  num_levels = 1 for fmap1, 4 for fmap2.  D must be even. */
+int raftcorr_alt_pack(const float* fmap, int B, int D, int H, int W, int num_levels, void* const* out_levels,
+                      void* stream);
+
 /* fmap1_grad/fmap2_grad must be zero-filled by the caller (accumulated with atomics);
  * coords_grad may be NULL.  The reference returns coords_grad as all zeros
  * (correlation_kernel.cu:130,307,323); this library fills it (documented superset). */

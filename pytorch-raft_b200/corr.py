@@ -126,38 +126,56 @@ class AlternateCorrBlock:
         if precision not in (None, "bf16", "fp32"):
             raise ValueError("AlternateCorrBlock precision must be 'bf16' or 'fp32'")
         self._precision = precision or "bf16"
-        self.pyramid = [(fmap1, fmap2)]
-        for _ in range(self.num_levels):
-            fmap1 = F.avg_pool2d(fmap1, 2, stride=2)
-            fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
-            self.pyramid.append((fmap1, fmap2))
-        self._f1 = self.pyramid[0][0].permute(0, 2, 3, 1).contiguous()
-        self._f2 = [self.pyramid[i][1].permute(0, 2, 3, 1).contiguous() for i in range(num_levels)]
+        self._fmaps = (fmap1, fmap2)
+        self._pyramid = None          # the reference's list of pooled NCHW pairs, made when somebody reads it
+        self._nhwc = None             # fp32 NHWC copies (fp32 kernels, autograd)
         self._f1_bf16 = self._f2_bf16 = None
-        dim = self._f1.shape[-1]
+        dim = fmap1.shape[1]
         if self._precision == "bf16" and dim % 8 == 0 and dim <= 256 and radius in (3, 4):
-            self._f1_bf16 = self._f1.detach().to(torch.bfloat16)
-            self._f2_bf16 = [t.detach().to(torch.bfloat16) for t in self._f2]
+            # one launch per fmap: pooled, channels-last, bfloat16 (csrc/alt_pack.cu)
+            self._f1_bf16 = ops.alt_pack(fmap1.detach(), 1)[0]
+            self._f2_bf16 = ops.alt_pack(fmap2.detach(), num_levels)
+
+    @property
+    def pyramid(self):
+        """core/corr.py:68-72: [(fmap1, fmap2)] followed by num_levels 2x2 mean-poolings of both."""
+        if self._pyramid is None:
+            fmap1, fmap2 = self._fmaps
+            self._pyramid = [(fmap1, fmap2)]
+            for _ in range(self.num_levels):
+                fmap1 = F.avg_pool2d(fmap1, 2, stride=2)
+                fmap2 = F.avg_pool2d(fmap2, 2, stride=2)
+                self._pyramid.append((fmap1, fmap2))
+        return self._pyramid
+
+    def _fp32_nhwc(self):
+        """fmap1 and the pooled fmap2 levels channels-last in fp32 (the copies core/corr.py:82-83 makes per call)."""
+        if self._nhwc is None:
+            pyr = self.pyramid
+            self._nhwc = (pyr[0][0].permute(0, 2, 3, 1).contiguous(),
+                          [pyr[i][1].permute(0, 2, 3, 1).contiguous() for i in range(self.num_levels)])
+        return self._nhwc
 
     def __call__(self, coords):
-        dim = self._f1.shape[-1]
+        dim = self._fmaps[0].shape[1]
         scale = 1.0 / math.sqrt(dim)
-        graph = torch.is_grad_enabled() and (coords.requires_grad or self._f1.requires_grad
-                                             or self._f2[0].requires_grad)
+        graph = torch.is_grad_enabled() and (coords.requires_grad or self._fmaps[0].requires_grad
+                                             or self._fmaps[1].requires_grad)
         if self._f1_bf16 is not None and not graph:
             return ops.alt_fused_forward(self._f1_bf16, self._f2_bf16, coords, self.radius, self._coord_mode, scale)
+        f1, f2 = self._fp32_nhwc()
         if self._f1_bf16 is not None:
             holder = {"f1_bf16": self._f1_bf16, "f2_bf16": self._f2_bf16}
-            return ops.AltFusedFn.apply(coords, self._f1, holder, self.radius, self._coord_mode, scale, *self._f2)
+            return ops.AltFusedFn.apply(coords, f1, holder, self.radius, self._coord_mode, scale, *f2)
         coords = coords.permute(0, 2, 3, 1)
         B, H, W, _ = coords.shape
         corr_list = []
         for i in range(self.num_levels):
             coords_i = (coords / 2 ** i).reshape(B, 1, H, W, 2).contiguous()
             if graph:
-                corr = ops.AltFn.apply(self._f1, self._f2[i], coords_i, self.radius, self._coord_mode, scale)
+                corr = ops.AltFn.apply(f1, f2[i], coords_i, self.radius, self._coord_mode, scale)
             else:
-                corr = ops.alt_forward(self._f1, self._f2[i], coords_i, self.radius, self._coord_mode, scale)
+                corr = ops.alt_forward(f1, f2[i], coords_i, self.radius, self._coord_mode, scale)
             corr_list.append(corr.squeeze(1))
         corr = torch.stack(corr_list, dim=1)
         return corr.reshape(B, -1, H, W)

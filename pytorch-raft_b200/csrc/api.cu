@@ -44,6 +44,7 @@ int launch_build_tc_noalloc(const float* f1, const float* f2, int B, int D, int 
                             const raftcorr_level* levels, int precision, cudaStream_t stream);
 int launch_build_tc16(const float* f1, const float* f2, int B, int D, int H, int W, int L,
                       const raftcorr_level16* levels, void* ws, int64_t ws_bytes, cudaStream_t stream);
+int launch_alt_pack(const float* fmap, int B, int D, int H, int W, int L, void* const* out_levels, cudaStream_t stream);
 int lookup16_group_log2(int level);   // lookup16.cu: the lookup fetches the windows of 2^g neighbouring queries as one box
 int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coords, float* out, int B, int H, int W,
                         int r, int mode, cudaStream_t stream);
@@ -229,6 +230,19 @@ int raftcorr_lookup16_fwd(const raftcorr_level16* levels, int num_levels, const 
   RC_REQUIRE(valid_mode(coord_mode), "lookup16_fwd: coord_mode=%d", coord_mode);
   if (int rc = check_levels16(levels, num_levels, H, W, "lookup16_fwd")) return rc;
   return launch_lookup16_fwd(levels, num_levels, coords, out, B, H, W, radius, coord_mode, (cudaStream_t)stream);
+}
+
+int raftcorr_alt_pack(const float* fmap, int B, int D, int H, int W, int num_levels, void* const* out_levels,
+                      void* stream) {
+  RC_REQUIRE(fmap && out_levels, "alt_pack: NULL pointer");
+  RC_REQUIRE(B >= 0 && D >= 1 && H >= 1 && W >= 1, "alt_pack: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
+  RC_REQUIRE(num_levels >= 1 && num_levels <= RAFTCORR_MAX_LEVELS, "alt_pack: num_levels=%d", num_levels);
+  for (int l = 0; l < num_levels; ++l) {
+    RC_REQUIRE((H >> l) >= 1 && (W >> l) >= 1, "alt_pack: level %d of %dx%d is empty", l, H, W);
+    RC_REQUIRE(out_levels[l] != nullptr && !(reinterpret_cast<uintptr_t>(out_levels[l]) & 3),
+               "alt_pack: out_levels[%d] is NULL or not 4-byte aligned", l);
+  }
+  return launch_alt_pack(fmap, B, D, H, W, num_levels, out_levels, (cudaStream_t)stream);
 }
 
 int raftcorr_lookup_fwd(const raftcorr_level* levels, int num_levels, const float* coords,

@@ -71,6 +71,7 @@ SIGNATURES = {
                                                                               ctypes.c_void_p]),
     "raftcorr_alt_fused_fwd": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), c_float_p, c_float_p] +
                                [ctypes.c_int] * 7 + [ctypes.c_float, ctypes.c_void_p]),
+    "raftcorr_alt_pack": (ctypes.c_int, [c_float_p] + [ctypes.c_int] * 5 + [ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p]),
     "raftcorr_alt_bwd": (ctypes.c_int, [c_float_p] * 7 + [ctypes.c_int] * 8 + [ctypes.c_float,
                                                                               ctypes.c_void_p]),
     "raftcorr_upsample_flow_fwd": (ctypes.c_int, [c_float_p] * 3 + [ctypes.c_int] * 3 + [ctypes.c_void_p]),

@@ -293,6 +293,20 @@ def alt_fused_forward(fmap1_bf16: torch.Tensor, fmap2_bf16: Sequence[torch.Tenso
     return out
 
 
+def alt_pack(fmap: torch.Tensor, num_levels: int) -> List[torch.Tensor]:
+    """(B,D,H,W) fp32 NCHW -> [(B, H>>l, W>>l, D) bfloat16 NHWC for l < num_levels], level l+1 = the 2x2 mean of level l
+    in fp32 (core/corr.py:64-72's avg_pool2d chain + the NHWC copies of corr.py:82-83 + the bf16 cast, one launch)."""
+    _require_cuda_f32(fmap, "fmap")
+    fmap = fmap.contiguous()
+    B, D, H, W = fmap.shape
+    outs = [torch.empty((B, H >> l, W >> l, D), dtype=torch.bfloat16, device=fmap.device) for l in range(num_levels)]
+    ptrs = (ctypes.c_void_p * num_levels)(*[t.data_ptr() for t in outs])
+    with _on_device(fmap.device):
+        _capi.check(_capi.lib().raftcorr_alt_pack(fmap.data_ptr(), B, D, H, W, num_levels, ptrs, _stream(fmap)),
+                    "raftcorr_alt_pack")
+    return outs
+
+
 def alt_backward(fmap1, fmap2, coords, corr_grad, radius: int, coord_mode=COORD_DIRECT,
                  scale: float = 1.0, want_coords: bool = True):
     B, H1, W1, C = fmap1.shape
