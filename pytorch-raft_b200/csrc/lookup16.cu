@@ -108,7 +108,7 @@ struct Lookup16Params {
   float* out;
   int B, H, W, tiles_x;
   long long tiles;
-  int debug;   // development switches (RAFTCORR_L16_DEBUG): bit 0 = skip the sampling (fill path only); bits 8.. = start skew
+  int debug;   // 0 in product builds; -DRAFTCORR_L16_DEV reads RAFTCORR_L16_DEBUG: bit 0 = skip the sampling (fill path only); bits 8.. = start skew
 };
 
 // box shapes: [level][one image / the level's group of images][wide: 2 or 3 blocks][tall: 3 or 4 block rows]
@@ -751,10 +751,10 @@ int launch_lookup16_fwd(const raftcorr_level16* levels, int L, const float* coor
   }
   p.coords = coords;
   p.out = out;
-  {
-    const char* dbg = getenv("RAFTCORR_L16_DEBUG");
-    p.debug = dbg ? atoi(dbg) : 0;
-  }
+  p.debug = 0;
+#ifdef RAFTCORR_L16_DEV   // development builds only (tools/build_variant.py dev -DRAFTCORR_L16_DEV): switches from the environment
+  if (const char* dbg = getenv("RAFTCORR_L16_DEBUG")) p.debug = atoi(dbg);
+#endif
   p.B = B;
   p.H = H;
   p.W = W;
