@@ -106,7 +106,7 @@ int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B
  *      y*W + x, so neighbours are neighbouring queries of a row, whose windows nearly coincide: the lookup fetches
  *      them as one box, and DRAM then sees pieces of G*128..192 bytes instead of G pieces 14 KB apart):
  *        byte  (n / G) * G*image_stride + (((y>>2)*blocks_x + (x>>3)) * G + n % G) * 64 + (y&3)*16 + (x&7)*2
- *      raftcorr_pyramid16_layout chooses it (levels 0 and 1, when H*W is a multiple of G); the lookup takes
+ *      raftcorr_pyramid16_layout chooses it (levels 0 and 1, when W is a multiple of G); the lookup takes
  *      either form per level, the build takes levels 0 and 1 both plain or both with interleave_log2 = 2 and
  *      the other levels plain.  Pixels of a block that lie outside the H x W image are stored as +0.0 (the lookup relies on it: they are grid_sample's zero
  *      padding).  Values: bf16 tcgen05 products, fp32 accumulation and pooling, one rounding to bf16 per stored

@@ -205,7 +205,9 @@ int raftcorr_pyramid16_layout(int B, int H, int W, int num_levels, raftcorr_leve
     levels[l].image_stride = (int64_t)levels[l].blocks_x * levels[l].blocks_y * 64;
     // levels 0 and 1 (images of several KB, windows = a few 128..192-byte pieces of them) keep the blocks of the
     // 2^g queries the lookup fetches together side by side: one DRAM piece of 2^g * 128..192 bytes instead of 2^g
-    levels[l].interleave_log2 = (l < 2 && ((long long)H * W) % (1 << lookup16_group_log2(l)) == 0) ? lookup16_group_log2(l) : 0;
+    // (W a multiple of the group size: every row of queries then starts a group, so the lookup's lane groups are the
+    // groups in memory; otherwise the plain layout, where any four neighbouring lanes can share a box)
+    levels[l].interleave_log2 = (l < 2 && W % (1 << lookup16_group_log2(l)) == 0) ? lookup16_group_log2(l) : 0;
     levels[l].reserved = 0;
     bytes_per_level[l] = (int64_t)B * H * W * levels[l].image_stride;
   }

@@ -36,7 +36,7 @@ def _padding_is_zero(pyr16):
     return True
 
 
-@pytest.mark.parametrize("size,interleave", [((1, 9, 21), None), ((2, 8, 22), None), ((2, 8, 22), False)])
+@pytest.mark.parametrize("size,interleave", [((1, 9, 21), None), ((2, 8, 24), None), ((2, 8, 24), False), ((2, 8, 22), (2, 2, 0))])
 def test_layout_matches_the_header_formula(size, interleave):
     """pixel (y, x) of image n at byte (n // G) * G * image_stride + (((y>>2)*blocks_x + (x>>3)) * G + n % G) * 64
     + (y&3)*16 + (x&7)*2, G = 2**interleave_log2 (include/raftcorr.h)."""
@@ -44,7 +44,7 @@ def test_layout_matches_the_header_formula(size, interleave):
     gen = torch.Generator().manual_seed(1)
     levels = [torch.randn(B * H * W, 1, max(H >> l, 1), max(W >> l, 1), generator=gen) for l in range(3)]
     pyr = ops.Pyramid16.from_dense(levels, B, H, W, interleave=interleave)
-    want_g = [2, 2, 0] if (H * W) % 4 == 0 and interleave is None else [0, 0, 0]
+    want_g = list(interleave) if isinstance(interleave, tuple) else [2, 2, 0] if W % 4 == 0 and interleave is None else [0, 0, 0]
     for l in range(3):
         d = pyr.desc[l]
         assert (d.blocks_x, d.blocks_y, d.image_stride) == ((d.W + 7) // 8, (d.H + 3) // 4, ((d.W + 7) // 8) * ((d.H + 3) // 4) * 64)
@@ -61,7 +61,7 @@ def test_layout_matches_the_header_formula(size, interleave):
 
 SHAPES = [(1, 64, 16, 18), (2, 32, 17, 23), (1, 128, 46, 62), (1, 8, 55, 96), (2, 16, 24, 40), (1, 24, 9, 33),
           (1, 16, 8, 8), (1, 40, 33, 65),
-          (2, 32, 10, 10), (3, 16, 12, 14)]   # H*W % 4 == 0 but % 32 != 0: interleaved levels, tiles that end mid-warp
+          (2, 32, 10, 12), (3, 16, 9, 20)]   # W % 4 == 0 but H*W % 32 != 0: interleaved levels, tiles that end mid-warp
 
 
 @pytest.mark.parametrize("interleave", [None, False])
@@ -73,7 +73,7 @@ def test_build16_against_oracle_and_fp32_pyramid(shape, interleave):
     f2 = torch.randn(B, D, H, W, generator=gen)
     pyr16 = ops.build_pyramid(f1.cuda(), f2.cuda(), 4, "bf16", storage="bf16", interleave=interleave)
     assert isinstance(pyr16, ops.Pyramid16)
-    assert pyr16.desc[0].interleave_log2 == (2 if interleave is None and (H * W) % 4 == 0 else 0)
+    assert pyr16.desc[0].interleave_log2 == (2 if interleave is None and W % 4 == 0 else 0)
     want = oracle.build_pyramid(f1, f2, 4)
     wide = ops.build_pyramid(f1.cuda(), f2.cuda(), 4, "bf16", storage="fp32")
     for l in range(4):
@@ -109,9 +109,11 @@ def test_build16_overwrites_stale_padding():
 @pytest.mark.parametrize("kind", KINDS)
 @pytest.mark.parametrize("case", [(1, 16, 18, 4), (2, 17, 23, 3), (1, 46, 62, 4), (3, 9, 33, 4), (1, 16, 95, 3), (1, 16, 16, 4),
                                   (6, 40, 70, 4)])   # the last one: several tiles per CTA, the rings wrap
-@pytest.mark.parametrize("interleave", [None, False])
+@pytest.mark.parametrize("interleave", [None, False, (2, 2, 0, 0)])
 def test_lookup16_bit_exact_against_oracle(case, kind, interleave):
     B, H, W, r = case
+    if isinstance(interleave, tuple) and (B * H * W) % 4 != 0:
+        pytest.skip("an interleaved level needs a multiple of four images")
     gen = torch.Generator().manual_seed(H * 100 + W + r)
     levels = [torch.randn(B * H * W, 1, H >> l, W >> l, generator=gen) for l in range(4)]
     pyr = ops.Pyramid16.from_dense(levels, B, H, W, interleave=interleave)
