@@ -87,7 +87,7 @@ static int check_levels(const raftcorr_level* levels, int L, int H, int W, const
   return 0;
 }
 
-static int check_levels16(const raftcorr_level16* levels, int L, int H, int W, const char* what) {
+static int check_levels16(const raftcorr_level16* levels, int L, int H, int W, const char* what, long long images = 0) {
   RC_REQUIRE(levels != nullptr, "%s: levels is NULL", what);
   RC_REQUIRE(L >= 1 && L <= RAFTCORR_MAX_LEVELS, "%s: num_levels=%d not in [1,%d]", what, L, RAFTCORR_MAX_LEVELS);
   for (int l = 0; l < L; ++l) {
@@ -103,6 +103,8 @@ static int check_levels16(const raftcorr_level16* levels, int L, int H, int W, c
                "%s: levels[%d].image_stride must be a multiple of 64 and >= blocks_x*blocks_y*64", what, l);
     RC_REQUIRE(v.interleave_log2 >= 0 && v.interleave_log2 <= 3, "%s: levels[%d].interleave_log2=%d not in [0,3]", what, l,
                v.interleave_log2);
+    RC_REQUIRE(v.interleave_log2 == 0 || images % (1LL << v.interleave_log2) == 0,
+               "%s: levels[%d] interleaves 2^%d images, B*H*W=%lld is not a multiple", what, l, v.interleave_log2, images);
     RC_REQUIRE(v.interleave_log2 == 0 || v.image_stride == (int64_t)v.blocks_x * v.blocks_y * 64,
                "%s: levels[%d]: an interleaved level needs image_stride == blocks_x*blocks_y*64", what, l);
   }
@@ -220,7 +222,7 @@ int raftcorr_build_pyramid16(const float* fmap1, const float* fmap2, int B, int 
   RC_REQUIRE(fmap1 && fmap2, "build_pyramid16: fmap pointer is NULL");
   RC_REQUIRE(B >= 0 && D >= 1 && H >= 1 && W >= 1, "build_pyramid16: bad sizes B=%d D=%d H=%d W=%d", B, D, H, W);
   RC_REQUIRE((long long)H * W <= (1 << 24), "build_pyramid16: fmap too large");
-  if (int rc = check_levels16(levels, num_levels, H, W, "build_pyramid16")) return rc;
+  if (int rc = check_levels16(levels, num_levels, H, W, "build_pyramid16", (long long)B * H * W)) return rc;
   return launch_build_tc16(fmap1, fmap2, B, D, H, W, num_levels, levels, workspace, workspace_bytes,
                            (cudaStream_t)stream);
 }
@@ -230,7 +232,7 @@ int raftcorr_lookup16_fwd(const raftcorr_level16* levels, int num_levels, const 
   RC_REQUIRE(coords && out, "lookup16_fwd: coords/out is NULL");
   RC_REQUIRE(B >= 0 && H >= 1 && W >= 1, "lookup16_fwd: bad sizes B=%d H=%d W=%d", B, H, W);
   RC_REQUIRE(valid_mode(coord_mode), "lookup16_fwd: coord_mode=%d", coord_mode);
-  if (int rc = check_levels16(levels, num_levels, H, W, "lookup16_fwd")) return rc;
+  if (int rc = check_levels16(levels, num_levels, H, W, "lookup16_fwd", (long long)B * H * W)) return rc;
   return launch_lookup16_fwd(levels, num_levels, coords, out, B, H, W, radius, coord_mode, (cudaStream_t)stream);
 }
 

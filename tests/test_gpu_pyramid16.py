@@ -244,3 +244,26 @@ def test_lookup16_rejects_what_it_does_not_cover():
     pyr = ops.Pyramid16(1, 16, 16, 4, "cuda", zero=True)
     rc = lib.raftcorr_build_pyramid16(f.data_ptr(), f.data_ptr(), 1, 12, 16, 16, 4, pyr.desc, None, 0, None)
     assert rc == -2 and b"D % 8" in lib.raftcorr_last_error()
+
+
+def test_interleaved_levels_are_checked():
+    """interleave_log2 outside [0, 3], an image count that is no multiple of the group, a build asked for a layout
+    it does not write: refused with RAFTCORR_E_INVALID / RAFTCORR_E_UNSUPPORTED before any launch."""
+    lib = _capi.lib()
+    c = torch.zeros(1, 2, 9, 21, device="cuda")
+    out = torch.empty(1, 4 * 81, 9, 21, device="cuda")
+    pyr = ops.Pyramid16(1, 9, 21, 4, "cuda", zero=True)        # 189 images: plain layout
+    pyr.desc[0].interleave_log2 = 2
+    rc = lib.raftcorr_lookup16_fwd(pyr.desc, 4, c.data_ptr(), out.data_ptr(), 1, 9, 21, 4, 0, None)
+    assert rc == -1 and b"not a multiple" in lib.raftcorr_last_error()
+    pyr.desc[0].interleave_log2 = 5
+    rc = lib.raftcorr_lookup16_fwd(pyr.desc, 4, c.data_ptr(), out.data_ptr(), 1, 9, 21, 4, 0, None)
+    assert rc == -1 and b"interleave_log2" in lib.raftcorr_last_error()
+    f = torch.zeros(1, 16, 16, 16, device="cuda")
+    pyr = ops.Pyramid16(1, 16, 16, 4, "cuda", zero=True, interleave=(2, 0, 0, 0))
+    ws = torch.empty(1 << 20, dtype=torch.uint8, device="cuda")
+    rc = lib.raftcorr_build_pyramid16(f.data_ptr(), f.data_ptr(), 1, 16, 16, 16, 4, pyr.desc, ws.data_ptr(), ws.numel(), None)
+    assert rc == -2 and b"both" in lib.raftcorr_last_error()
+    pyr = ops.Pyramid16(1, 16, 16, 4, "cuda", zero=True, interleave=(2, 2, 2, 0))
+    rc = lib.raftcorr_build_pyramid16(f.data_ptr(), f.data_ptr(), 1, 16, 16, 16, 4, pyr.desc, ws.data_ptr(), ws.numel(), None)
+    assert rc == -2 and b"only levels 0 and 1" in lib.raftcorr_last_error()
