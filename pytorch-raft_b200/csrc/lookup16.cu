@@ -192,23 +192,23 @@ __device__ __noinline__ float pixel16_global(const Level16Dev& lv, long long img
   return bf16_bits_to_float(*reinterpret_cast<const unsigned short*>(p));
 }
 
-// One query's samples at one level for x taps [i_begin, i_end), out of its slot.
+// One query's samples at one level out of its part of the unit buffer.
 //
-// Tap j of an axis sits on pixel m + j + e_j with m = min_j(i0_j - j).  Normally every e_j is 0 (kFlips = false):
-// the footprint is a dense (rd+1) x (rd+1) patch, each pixel is loaded once, and the right-hand column of x tap i is
-// carried over as the left-hand column of tap i+1.  On the integer grid (RAFT's first iteration) the reference's
-// coordinate round trip moves floor() down by one on ~8 % of the taps: e_j is then 0 or 1 per lane and tap
-// (kFlips = true), the patch grows by one row and one column, it is still loaded once, and which of two
-// neighbouring rows / columns a tap uses is a per-lane select on registers.
+// Tap j of an axis sits on pixel m + j + e_j with m = min_j(i0_j - j).  Normally every e_j is 0: the footprint is a
+// dense (rd+1) x (rd+1) patch, each pixel is loaded once, and the right-hand column of x tap i is carried over as the
+// left-hand column of tap i+1 (sample_unit_dense2 below).  On the integer grid (RAFT's first iteration) the
+// reference's coordinate round trip moves floor() down by one on ~8 % of the taps: e_j is then 0 or 1 per lane and
+// tap, the patch grows by one row and one column, it is still loaded once, and which of two neighbouring rows /
+// columns a tap uses is a per-lane select on registers (sample_unit_flips).
 //
 // The x-tap loop is a real loop (the taps are recomputed from the loop counter, ~14 instructions): fully unrolled,
-// the variants of this routine came to 10k SASS instructions and the warps of an SM — each in a different variant
+// the variants of these routines came to 10k SASS instructions and the warps of an SM — each in a different variant
 // or phase — spent 40 % of their issue slots waiting for the instruction cache.
-template <int R, int kMode, bool kFlips, bool kAllLive>
-__device__ __forceinline__ void sample_unit(uint32_t slot_addr, uint32_t swz_mask, int cshift, int bw, int bh, int bx0, int by0, int mx, int my,
-                                            float cxl, const Level16Dev& lv, const Tap (&ty)[2 * R + 1], int i_begin,
-                                            int i_end, float* optr, long long N, bool live) {
-  constexpr int rd = 2 * R + 1, kRows = rd + 1 + (kFlips ? 1 : 0);
+template <int R, int kMode>
+__device__ __forceinline__ void sample_unit_flips(uint32_t slot_addr, uint32_t swz_mask, int cshift, int bw, int bh, int bx0,
+                                                  int by0, int mx, int my, float cxl, const Level16Dev& lv,
+                                                  const Tap (&ty)[2 * R + 1], float* optr, long long N, bool live) {
+  constexpr int rd = 2 * R + 1, kRows = rd + 2;
   const int rowpitch = bw << cshift;   // bytes per block row of the box (a block column is 1 << cshift bytes wide)
   auto px = [&](uint32_t row, uint32_t col) -> float {
     unsigned short v;
@@ -220,18 +220,16 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, uint32_t swz_mas
     const float nw = __fmul_rn(s_, e_), ne = __fmul_rn(s_, w_), sw = __fmul_rn(n_, e_), se = __fmul_rn(n_, w_);
     return __fmaf_rn(vse, se, __fmaf_rn(vsw, sw, __fmaf_rn(vne, ne, __fmul_rn(vnw, nw))));
   };
-  // Patch rows / columns that no tap of this lane uses may fall outside the box (flips only): their addresses are
-  // clamped into the slot; the values are loaded but never selected.
+  // Patch rows / columns that no tap of this lane uses may fall outside the box: their addresses are clamped into
+  // the lane's part of the buffer; the values are loaded but never selected.
   uint32_t rows[kRows];
 #pragma unroll
   for (int r = 0; r < kRows; ++r) {
-    int yy = my + r - 4 * by0;
-    if (kFlips) yy = max(0, min(yy, 4 * bh - 1));
+    const int yy = max(0, min(my + r - 4 * by0, 4 * bh - 1));
     rows[r] = slot_addr + (uint32_t)((yy >> 2) * rowpitch + (yy & 3) * 16);
   }
   auto col_off = [&](int c) {
-    int xx = mx + c - 8 * bx0;
-    if (kFlips) xx = max(0, min(xx, 8 * bw - 1));
+    const int xx = max(0, min(mx + c - 8 * bx0, 8 * bw - 1));
     return (uint32_t)(((xx >> 3) << cshift) + (xx & 7) * 2);
   };
   float fy[rd], sy[rd];
@@ -240,64 +238,68 @@ __device__ __forceinline__ void sample_unit(uint32_t slot_addr, uint32_t swz_mas
   for (int j = 0; j < rd; ++j) {
     fy[j] = ty[j].frac;
     sy[j] = __fsub_rn(1.0f, fy[j]);
-    ey[j] = kFlips && (ty[j].i0 - j) != my;
+    ey[j] = (ty[j].i0 - j) != my;
   }
   float c0[kRows], c1[kRows], c2[kRows];
   {
-    const uint32_t a = col_off(i_begin), b = col_off(i_begin + 1);
+    const uint32_t a = col_off(0), b = col_off(1);
 #pragma unroll
     for (int r = 0; r < kRows; ++r) {
       c0[r] = px(rows[r], a);
-      if (kFlips) c1[r] = px(rows[r], b);
+      c1[r] = px(rows[r], b);
     }
   }
-  float* o = optr + (long long)(i_begin * rd) * N;
+  float* o = optr;
 #pragma unroll kUnroll16
-  for (int i = i_begin; i < i_end; ++i) {
+  for (int i = 0; i < rd; ++i) {
     const Tap t = make_tap_fast(cxl, (float)(i - R), lv.sm1x, lv.invx, lv.halfx, kMode);
     const float fx = t.frac, ex = __fsub_rn(1.0f, fx);
+    const uint32_t c = col_off(i + 2);
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) c2[r] = px(rows[r], c);
+    const bool flip = (t.i0 - i) != mx;
     float lft[kRows], rgt[kRows];
-    if constexpr (kFlips) {
-      const uint32_t c = col_off(i + 2);
 #pragma unroll
-      for (int r = 0; r < kRows; ++r) c2[r] = px(rows[r], c);
-      const bool flip = (t.i0 - i) != mx;
-#pragma unroll
-      for (int r = 0; r < kRows; ++r) {
-        lft[r] = flip ? c1[r] : c0[r];
-        rgt[r] = flip ? c2[r] : c1[r];
-      }
-    } else {
-      const uint32_t c = col_off(i + 1);
-#pragma unroll
-      for (int r = 0; r < kRows; ++r) {
-        c1[r] = px(rows[r], c);
-        lft[r] = c0[r];
-        rgt[r] = c1[r];
-      }
+    for (int r = 0; r < kRows; ++r) {
+      lft[r] = flip ? c1[r] : c0[r];
+      rgt[r] = flip ? c2[r] : c1[r];
     }
+    // outputs j and j + 1 share the packed fp32x2 instructions (the same IEEE operations, two at a time)
+    const float2 e2 = make_float2(ex, ex), w2 = make_float2(fx, fx);
 #pragma unroll
-    for (int j = 0; j < rd; ++j) {
-      float tl = lft[j], bl = lft[j + 1], tr = rgt[j], br = rgt[j + 1];
-      if constexpr (kFlips) {
-        tl = ey[j] ? lft[j + 1] : lft[j];
-        bl = ey[j] ? lft[j + 2] : lft[j + 1];
-        tr = ey[j] ? rgt[j + 1] : rgt[j];
-        br = ey[j] ? rgt[j + 2] : rgt[j + 1];
+    for (int j = 0; j + 1 < rd; j += 2) {
+      const float2 tl = make_float2(ey[j] ? lft[j + 1] : lft[j], ey[j + 1] ? lft[j + 2] : lft[j + 1]);
+      const float2 bl = make_float2(ey[j] ? lft[j + 2] : lft[j + 1], ey[j + 1] ? lft[j + 3] : lft[j + 2]);
+      const float2 tr = make_float2(ey[j] ? rgt[j + 1] : rgt[j], ey[j + 1] ? rgt[j + 2] : rgt[j + 1]);
+      const float2 br = make_float2(ey[j] ? rgt[j + 2] : rgt[j + 1], ey[j + 1] ? rgt[j + 3] : rgt[j + 2]);
+      const float2 n2 = make_float2(fy[j], fy[j + 1]), s2 = make_float2(sy[j], sy[j + 1]);
+      float2 acc = __fmul2_rn(tl, __fmul2_rn(s2, e2));
+      acc = __ffma2_rn(tr, __fmul2_rn(s2, w2), acc);
+      acc = __ffma2_rn(bl, __fmul2_rn(n2, e2), acc);
+      acc = __ffma2_rn(br, __fmul2_rn(n2, w2), acc);
+      if (live) {
+        __stcs(o, acc.x);
+        __stcs(o + N, acc.y);
       }
+      o += 2 * N;
+    }
+    {
+      constexpr int j = rd - 1;
+      const float tl = ey[j] ? lft[j + 1] : lft[j], bl = ey[j] ? lft[j + 2] : lft[j + 1];
+      const float tr = ey[j] ? rgt[j + 1] : rgt[j], br = ey[j] ? rgt[j + 2] : rgt[j + 1];
       const float v = combine(tl, tr, bl, br, fx, ex, fy[j], sy[j]);
-      if (kAllLive || live) __stcs(o, v);
+      if (live) __stcs(o, v);
       o += N;
     }
 #pragma unroll
     for (int r = 0; r < kRows; ++r) {
       c0[r] = c1[r];
-      if (kFlips) c1[r] = c2[r];
+      c1[r] = c2[r];
     }
   }
 }
 
-// The dense footprint again (kFlips = false), two outputs per floating-point instruction: sm_100's packed fp32
+// The dense footprint, two outputs per floating-point instruction: sm_100's packed fp32
 // operations (fma.rn.f32x2 & co.: each half is the IEEE operation, so the bits do not change) halve the issue slots
 // of the weight products and the four-term sum, which are 45 % of this routine.  Outputs j and j + 2 of an x tap
 // share an instruction: their upper-left pixels are patch rows (j, j + 2) and their lower-left ones (j + 1, j + 3),
@@ -592,7 +594,7 @@ lookup16_kernel(const __grid_constant__ Lookup16Params p, const __grid_constant_
     } else if (all_chain) {
       sample_unit_dense2<R, kMode, false>(slot_addr, swz_mask, cshift, bw, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, (unsigned)N, live);
     } else {
-      sample_unit<R, kMode, true, false>(slot_addr, swz_mask, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, ib, ie, cur.optr, N, live);
+      sample_unit_flips<R, kMode>(slot_addr, swz_mask, cshift, bw, bh, w.bx0, w.by0, mx, my, cur.cxl, lv, ty, cur.optr, N, live);
     }
     L16_TICK(t3);
     if (more) {
