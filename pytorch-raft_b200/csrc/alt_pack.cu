@@ -35,26 +35,36 @@ struct AltPackParams {
   int B, D, H, W, L;
 };
 
-// pixels of level l covered by the tile, stored for channels c0 .. c0+63 (lane = channel pair, warp = pixel)
-__device__ __forceinline__ void store_level(const float* src, int pitch, int tw, int th, __nv_bfloat16* out, int b, int Hl,
-                                            int Wl, int D, int y0, int x0, int c0, int warp, int lane) {
+// pixels of level l covered by the tile (TW x TH of them), stored for channels c0 .. c0+63: lane = channel pair, one
+// pixel per warp and step; pixel p = warp + 8 i sits at row i / (TW / 8), column warp + 8 (i % (TW / 8)) of the tile
+template <int TW, int TH>
+__device__ __forceinline__ void store_level(const float* src, int pitch, __nv_bfloat16* out, int b, int Hl, int Wl, int D,
+                                            int y0, int x0, int c0, int warp, int lane) {
   const int c = c0 + 2 * lane;
-  for (int p = warp; p < tw * th; p += 8) {
-    const int py = p / tw, px = p - py * tw;
-    const int y = y0 + py, x = x0 + px;
-    if (y >= Hl || x >= Wl || c >= D) continue;
-    const float lo = src[(2 * lane) * pitch + p], hi = src[(2 * lane + 1) * pitch + p];
-    *reinterpret_cast<uint32_t*>(out + (((long long)b * Hl + y) * Wl + x) * D + c) = pack_bf16x2(lo, hi);
+  if (c >= D || y0 >= Hl || x0 >= Wl) return;
+  __nv_bfloat16* base = out + (((long long)b * Hl + y0) * Wl + x0) * D + c;
+  const float* s0 = src + (2 * lane) * pitch;
+  constexpr int kPer = TW >= 8 ? TW / 8 : 1;             // steps per tile row
+  constexpr int kSteps = (TW * TH + 7) / 8;
+#pragma unroll
+  for (int i = 0; i < kSteps; ++i) {
+    const int py = i / kPer, px = warp + 8 * (i % kPer);
+    if (TW < 8 && warp >= TW) continue;
+    if (y0 + py >= Hl || x0 + px >= Wl) continue;
+    const int q = py * TW + px;
+    *reinterpret_cast<uint32_t*>(base + ((long long)py * Wl + px) * D) = pack_bf16x2(s0[q], s0[pitch + q]);
   }
 }
 
-__device__ __forceinline__ void pool_level(const float* src, int spitch, int sw, float* dst, int dpitch, int dw, int dh,
-                                           int tid) {
-  for (int k = tid; k < kPCh * dw * dh; k += 256) {
-    const int c = k / (dw * dh), p = k - c * (dw * dh);
-    const int py = p / dw, px = p - py * dw;
-    const float* s = src + c * spitch + (2 * py) * sw + 2 * px;
-    dst[c * dpitch + p] = (((s[0] + s[1]) + s[sw]) + s[sw + 1]) * 0.25f;   // ATen avg_pool2d: row-major sum, then / 4
+template <int SW, int DW, int DH>
+__device__ __forceinline__ void pool_level(const float* src, int spitch, float* dst, int dpitch, int tid) {
+  constexpr int kPix = DW * DH;
+#pragma unroll
+  for (int k0 = 0; k0 < kPCh * kPix; k0 += 256) {
+    const int k = k0 + tid, c = k / kPix, q = k % kPix;
+    const int py = q / DW, px = q % DW;
+    const float* s = src + c * spitch + (2 * py) * SW + 2 * px;
+    dst[c * dpitch + q] = (((s[0] + s[1]) + s[SW]) + s[SW + 1]) * 0.25f;   // ATen avg_pool2d: row-major sum, then / 4
   }
 }
 
@@ -68,31 +78,36 @@ __global__ void __launch_bounds__(256) alt_pack_kernel(const AltPackParams p) {
   const int slices = (p.D + kPCh - 1) / kPCh;
   const int b = blockIdx.z / slices, c0 = (blockIdx.z - b * slices) * kPCh;
   const int y0 = blockIdx.y * kPTileY, x0 = blockIdx.x * kPTileX;
-  // rows of the tile: (channel, row) pairs, one per warp and step; lane = column
-#pragma unroll 16
-  for (int r = warp; r < kPCh * kPTileY; r += 8) {
-    const int c = r / kPTileY, y = r - c * kPTileY;
-    float v = 0.0f;
-    if (c0 + c < p.D && y0 + y < p.H && x0 + lane < p.W)
-      v = __ldg(p.in + (((long long)b * p.D + c0 + c) * p.H + y0 + y) * p.W + x0 + lane);
-    t0[c * kPPitch + y * kPTileX + lane] = v;
+  // warp w loads row w of the tile for every channel of the slice (lane = column); all 64 row segments are requested
+  // before the first is used
+  {
+    const bool ok = (y0 + warp < p.H) & (x0 + lane < p.W);
+    const int nch = min(kPCh, p.D - c0);
+    const long long cstride = (long long)p.H * p.W;
+    const float* src = p.in + (((long long)b * p.D + c0) * p.H + y0 + warp) * p.W + x0 + lane;
+    float v[kPCh];
+#pragma unroll
+    for (int k = 0; k < kPCh; ++k) v[k] = (ok && k < nch) ? __ldcs(src + k * cstride) : 0.0f;
+    float* d = t0 + warp * kPTileX + lane;
+#pragma unroll
+    for (int k = 0; k < kPCh; ++k) d[k * kPPitch] = v[k];
   }
   __syncthreads();
-  store_level(t0, kPPitch, kPTileX, kPTileY, p.out[0], b, p.H, p.W, p.D, y0, x0, c0, warp, lane);
+  store_level<32, 8>(t0, kPPitch, p.out[0], b, p.H, p.W, p.D, y0, x0, c0, warp, lane);
   if (p.L > 1) {
-    pool_level(t0, kPPitch, kPTileX, t1, 4 * 16 + 1, 16, 4, tid);
+    pool_level<32, 16, 4>(t0, kPPitch, t1, 4 * 16 + 1, tid);
     __syncthreads();
-    store_level(t1, 4 * 16 + 1, 16, 4, p.out[1], b, p.H >> 1, p.W >> 1, p.D, y0 >> 1, x0 >> 1, c0, warp, lane);
+    store_level<16, 4>(t1, 4 * 16 + 1, p.out[1], b, p.H >> 1, p.W >> 1, p.D, y0 >> 1, x0 >> 1, c0, warp, lane);
   }
   if (p.L > 2) {
-    pool_level(t1, 4 * 16 + 1, 16, t2, 2 * 8 + 1, 8, 2, tid);
+    pool_level<16, 8, 2>(t1, 4 * 16 + 1, t2, 2 * 8 + 1, tid);
     __syncthreads();
-    store_level(t2, 2 * 8 + 1, 8, 2, p.out[2], b, p.H >> 2, p.W >> 2, p.D, y0 >> 2, x0 >> 2, c0, warp, lane);
+    store_level<8, 2>(t2, 2 * 8 + 1, p.out[2], b, p.H >> 2, p.W >> 2, p.D, y0 >> 2, x0 >> 2, c0, warp, lane);
   }
   if (p.L > 3) {
-    pool_level(t2, 2 * 8 + 1, 8, t3, 1 * 4 + 1, 4, 1, tid);
+    pool_level<8, 4, 1>(t2, 2 * 8 + 1, t3, 1 * 4 + 1, tid);
     __syncthreads();
-    store_level(t3, 1 * 4 + 1, 4, 1, p.out[3], b, p.H >> 3, p.W >> 3, p.D, y0 >> 3, x0 >> 3, c0, warp, lane);
+    store_level<4, 1>(t3, 1 * 4 + 1, p.out[3], b, p.H >> 3, p.W >> 3, p.D, y0 >> 3, x0 >> 3, c0, warp, lane);
   }
 }
 
