@@ -586,7 +586,7 @@ def main():
         dev1, dev2 = dev1.contiguous(memory_format=torch.channels_last), dev2.contiguous(memory_format=torch.channels_last)
     host_flow = torch.empty(BATCH_PER_GPU, 2, IMG_H, IMG_W).pin_memory()
     args.stock_convc1 = not args.tc_convc1
-    nhwc_lookup = args.channels_last or args.tc_convc1
+    nhwc_lookup = args.channels_last    # (--tc-convc1 reads the plain NCHW lookup: raftcorr_conv1x1_nchw_fwd)
     storage = "fp32" if nhwc_lookup else args.pyramid          # the channels-last lookup reads the fp32 pyramid
     from raftcorr_b200 import ops
     storage16 = ops.resolve_storage(storage, ops.resolve_precision(args.precision), 256, LEVELS, RADIUS) == "bf16"
@@ -768,7 +768,7 @@ def main():
                        build_precision=args.precision or "bf16", encoders="stock PyTorch/cuDNN fp32",
                        pyramid="bf16 in 4x8-pixel 64-byte blocks (raftcorr_level16)" if storage16 else "fp32 rows (raftcorr_level)",
                        convc1="stock torch conv2d + relu on an NCHW lookup (update.py unchanged)" if args.stock_convc1 else
-                       "raftcorr_conv1x1_nhwc_fwd (tf32 tcgen05, bias + ReLU epilogue) on a channels-last lookup",
+                       "raftcorr_conv1x1_nchw_fwd (tf32 tcgen05, MN-major activations, bias + ReLU epilogue) on the NCHW lookup",
                        upsample="stock torch ops (raft.py:72-83)" if args.stock_upsample else
                        "raftcorr_upsample_flow_fwd, every iteration like the reference",
                        memory_format="channels_last" if args.channels_last else "contiguous (NCHW, as the reference)"),

@@ -230,6 +230,11 @@ int64_t raftcorr_lookup_conv1x1_workspace_bytes(int B, int H, int W, int num_lev
  * out = act . weight^T + bias, optional ReLU. */
 int raftcorr_conv1x1_nhwc_fwd(const float* act, const float* weight, const float* bias, float* out, int B,
                               int pixels, int in_channels, int out_channels, int relu, void* stream);
+/* The same product on a plain NCHW activation tensor (B, in_channels, pixels) — what raftcorr_lookup_fwd and
+ * raftcorr_lookup16_fwd write: the pixel axis is the contiguous one, the tensor cores take it as an MN-major operand.
+ * out_channels <= 256. */
+int raftcorr_conv1x1_nchw_fwd(const float* act, const float* weight, const float* bias, float* out, int B,
+                              int pixels, int in_channels, int out_channels, int relu, void* stream);
 int raftcorr_lookup_conv1x1_fwd(const raftcorr_level* levels, int num_levels, const float* coords,
                                 const float* weight, const float* bias, float* out, int B, int H, int W,
                                 int radius, int coord_mode, int out_channels, int relu, void* workspace,

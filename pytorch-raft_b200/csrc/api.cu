@@ -65,7 +65,7 @@ int launch_tc_conv1x1(const float* weight, long long w_pitch, const float* act, 
                       int K, const float* bias, int relu, cudaStream_t stream);
 bool tc_gemm_available();
 int launch_conv1x1_tc(const float* weight, const float* act, float* out, int B, int M, int Nn, int K,
-                      const float* bias, int relu, cudaStream_t stream);
+                      const float* bias, int relu, cudaStream_t stream, int nchw = 0);
 int launch_alt_bwd(const float* f1, const float* f2, const float* coords, const float* gcorr,
                    float* g1, float* g2, float* gcoords, int B, int H1, int W1, int H2, int W2, int C,
                    int r, int mode, float scale, cudaStream_t stream);
@@ -388,6 +388,22 @@ int raftcorr_conv1x1_nhwc_fwd(const float* act, const float* weight, const float
   return launch_tc_conv1x1(weight, in_channels, act, in_channels, (long long)pixels * in_channels, out, pixels,
                            (long long)out_channels * pixels, B, out_channels, pixels, in_channels, bias, relu,
                            (cudaStream_t)stream);
+}
+
+int raftcorr_conv1x1_nchw_fwd(const float* act, const float* weight, const float* bias, float* out, int B,
+                              int pixels, int in_channels, int out_channels, int relu, void* stream) {
+  RC_REQUIRE(act && weight && out, "conv1x1_nchw_fwd: act/weight/out is NULL");
+  RC_REQUIRE(B >= 0 && pixels >= 1 && in_channels >= 1 && out_channels >= 1, "conv1x1_nchw_fwd: bad sizes");
+  if ((in_channels & 3) || (pixels & 3) || out_channels > 256 || !tc_gemm_available() ||
+      (reinterpret_cast<uintptr_t>(weight) & 15) || (reinterpret_cast<uintptr_t>(act) & 15) ||
+      (reinterpret_cast<uintptr_t>(out) & 15))
+    return raftcorr::fail(RAFTCORR_E_UNSUPPORTED,
+                          "conv1x1_nchw_fwd: needs in_channels %% 4 == 0, pixels %% 4 == 0, out_channels <= 256 (%d, %d, %d) "
+                          "and 16-byte aligned pointers", in_channels, pixels, out_channels);
+  const int rc = launch_conv1x1_tc(weight, act, out, B, out_channels, pixels, in_channels, bias, relu,
+                                   (cudaStream_t)stream, 1);
+  if (rc == 1) return raftcorr::fail(RAFTCORR_E_UNSUPPORTED, "conv1x1_nchw_fwd: shape not covered");
+  return rc;
 }
 
 int raftcorr_lookup_conv1x1_fwd(const raftcorr_level* levels, int num_levels, const float* coords,

@@ -9,6 +9,13 @@
 // and 8 x 55 tiles at cfg2 fill 148 SMs in 2.97 waves.  K-major fp32 operands, kind::tf32, fp32 accumulate;
 // bias + ReLU in the TMEM epilogue; TMA stores straight into NCHW.
 //
+// The samples may also come as the plain NCHW lookup (S[b][c][pix], what CorrBlock returns by default and what the
+// 16-bit lookup writes): the pixel axis is then contiguous, i.e. the B operand is MN-major — tcgen05 takes that for
+// tf32 (instruction-descriptor bit 16) in one layout only, the 128-byte swizzle with 32-byte atoms (TMA
+// SWIZZLE_128B_ATOM_32B, descriptor layout type 1; atom = 32 pixels x 4 channels): four TMA boxes of {32 pixels,
+// 32 channels} per stage, leading byte offset 4096 (next 32 pixels), stride byte offset 512 (next 4 channels), and
+// an MMA step (K = 8) advances the descriptor by 1024 bytes.
+//
 //   warp 0      TMA producer (3 stages of {W half 0, W half 1, 128 pixels} x 32 channels)
 //   warp 1      MMA issuer   (tcgen05.mma cta_group::1 kind::tf32, M128 N128, 2 x 2 accumulators)
 //   warps 2-9   epilogue     (warps 2-5 the first 128 output channels, 6-9 the second)
@@ -35,6 +42,7 @@ constexpr int kCThreads = 32 * (2 + kCEpiWarps);
 
 struct ConvParams {
   int B, M, Nn, k_blocks, halves, tiles_n;
+  int nchw;        // 1: activations are (B, K, pixels), the B operand is MN-major
   long long tiles;
   const float* bias;
   int relu;
@@ -87,7 +95,12 @@ conv1x1_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
           mbar_expect_tx(full_bar(s), (uint32_t)(p.halves * kCBytesA + kCBytesB));
           const uint32_t dst = smem_base + s * kCStageBytes;
           for (int h = 0; h < p.halves; ++h) tma_load_3d(dst + h * kCBytesA, &map_w, full_bar(s), kb * 32, h * kCM, 0);
-          tma_load_3d(dst + 2 * kCBytesA, &map_s, full_bar(s), kb * 32, nt * kCN, b);
+          if (p.nchw) {
+            for (int j = 0; j < kCN / 32; ++j)
+              tma_load_3d(dst + 2 * kCBytesA + j * 4096, &map_s, full_bar(s), nt * kCN + j * 32, kb * 32, b);
+          } else {
+            tma_load_3d(dst + 2 * kCBytesA, &map_s, full_bar(s), kb * 32, nt * kCN, b);
+          }
         }
       }
     }
@@ -104,12 +117,14 @@ conv1x1_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
           mbar_wait(full_bar(s), (it / kCStages) & 1);
           tc_fence_after();
           const uint32_t base = smem_base + s * kCStageBytes;
-          const uint64_t bdesc = make_smem_desc(base + 2 * kCBytesA);
+          // K-major: 32 bytes of K per step (+2 in the 16-byte address field); MN-major: one 1024-byte atom per step
+          const uint64_t bdesc = p.nchw ? make_smem_desc_mn32(base + 2 * kCBytesA, 4096, 512) : make_smem_desc(base + 2 * kCBytesA);
+          const uint64_t bstep = p.nchw ? (1024 >> 4) : 2;
           for (int h = 0; h < p.halves; ++h) {
             const uint64_t adesc = make_smem_desc(base + h * kCBytesA);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              tc_mma<true>(d_tmem + h * kCN, adesc + 2 * k, bdesc + 2 * k, p.idesc, (kb | k) != 0);
+              tc_mma<true>(d_tmem + h * kCN, adesc + 2 * k, bdesc + bstep * k, p.idesc, (kb | k) != 0);
           }
           tc_commit(empty_bar(s));
         }
@@ -184,7 +199,7 @@ conv1x1_tc_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_consta
 
 // returns 1 when this kernel does not apply (caller uses the generic plain-GEMM mode of build_tc.cu)
 int launch_conv1x1_tc(const float* weight, const float* act, float* out, int B, int M, int Nn, int K,
-                      const float* bias, int relu, cudaStream_t stream) {
+                      const float* bias, int relu, cudaStream_t stream, int nchw) {
   if (M > 2 * kCM || (K & 3) || (Nn & 3) || get_encode() == nullptr) return 1;
   if (B == 0) return 0;
   CUtensorMap map_w, map_s, map_o;
@@ -196,7 +211,14 @@ int launch_conv1x1_tc(const float* weight, const float* act, float* out, int B, 
                         CU_TENSOR_MAP_SWIZZLE_128B, "conv1x1 weight"))
       return rc;
   }
-  {
+  if (nchw) {
+    cuuint64_t dims[3] = {(cuuint64_t)Nn, (cuuint64_t)K, (cuuint64_t)B};
+    cuuint64_t strides[2] = {(cuuint64_t)Nn * 4, (cuuint64_t)Nn * K * 4};
+    cuuint32_t box[3] = {32, 32, 1};
+    if (int rc = encode(&map_s, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(act), dims, strides, box,
+                        CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, "conv1x1 activations (NCHW)"))
+      return rc;
+  } else {
     cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)Nn, (cuuint64_t)B};
     cuuint64_t strides[2] = {(cuuint64_t)K * 4, (cuuint64_t)Nn * K * 4};
     cuuint32_t box[3] = {32, kCN, 1};
@@ -222,7 +244,9 @@ int launch_conv1x1_tc(const float* weight, const float* act, float* out, int B, 
   p.tiles = (long long)B * p.tiles_n;
   p.bias = bias;
   p.relu = relu;
-  p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kCN >> 3) << 17) | ((uint32_t)(kCM >> 4) << 24);
+  p.nchw = nchw;
+  p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kCN >> 3) << 17) | ((uint32_t)(kCM >> 4) << 24) |
+            (nchw ? 1u << 16 : 0u);   // bit 16: B is MN-major
   int dev = 0;
   RC_CHECK_CUDA(cudaGetDevice(&dev));
   static std::atomic<int> sm_count[64];

@@ -221,6 +221,19 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
   return d;
 }
 
+// MN-major operand of 32-bit elements (tf32): the only layout the tensor cores take is the 128-byte swizzle with
+// 32-byte atoms (TMA: CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B; 32-byte chunk index ^= row & 3): rows of 128 B of MN,
+// atoms of 4 K-rows; lbo = bytes to the next 128 B of MN, sbo = bytes to the next 4 K-rows
+__device__ __forceinline__ uint64_t make_smem_desc_mn32(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(lbo >> 4) << 16;
+  d |= (uint64_t)(sbo >> 4) << 32;
+  d |= (uint64_t)1 << 46;            // descriptor version (Blackwell)
+  d |= (uint64_t)1 << 61;            // SWIZZLE_128B_BASE32B
+  return d;
+}
+
 // 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread
 __device__ __forceinline__ void tmem_ld_x32(uint32_t taddr, float* f) {
   uint32_t* v = reinterpret_cast<uint32_t*>(f);

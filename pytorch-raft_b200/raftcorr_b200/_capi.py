@@ -79,6 +79,7 @@ SIGNATURES = {
     "raftcorr_upflow8": (ctypes.c_int, [c_float_p] * 2 + [ctypes.c_int] * 3 + [ctypes.c_void_p]),
     "raftcorr_lookup_conv1x1_workspace_bytes": (ctypes.c_int64, [ctypes.c_int] * 5),
     "raftcorr_conv1x1_nhwc_fwd": (ctypes.c_int, [c_float_p] * 4 + [ctypes.c_int] * 5 + [ctypes.c_void_p]),
+    "raftcorr_conv1x1_nchw_fwd": (ctypes.c_int, [c_float_p] * 4 + [ctypes.c_int] * 5 + [ctypes.c_void_p]),
     "raftcorr_lookup_conv1x1_fwd": (ctypes.c_int, [ctypes.POINTER(Level), ctypes.c_int] + [c_float_p] * 4 +
                                     [ctypes.c_int] * 7 + [ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
 }

@@ -483,14 +483,17 @@ def lookup_conv1x1(pyr: Pyramid, coords: torch.Tensor, radius: int, weight: torc
 def conv1x1_channels_last(act: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None,
                           relu: bool = True) -> torch.Tensor:
     """relu(conv1x1(act)) for a (B, C, H, W) tensor held in channels_last memory (what ``lookup(...,
-    channels_last=True)`` returns) -> (B, out_channels, H, W) contiguous.  tcgen05 TF32 GEMM with the bias
-    and the ReLU in its epilogue.  Inference only."""
+    channels_last=True)`` returns) or plain NCHW (the default lookup) -> (B, out_channels, H, W) contiguous.
+    tcgen05 TF32 GEMM with the bias and the ReLU in its epilogue.  Inference only."""
     _require_cuda_f32(act, "act")
     _require_cuda_f32(weight, "weight")
     B, C, H, W = act.shape
-    if not act.is_contiguous(memory_format=torch.channels_last):
-        act = act.contiguous(memory_format=torch.channels_last)
     cout = weight.shape[0]
+    # a plain NCHW tensor (the default lookup, the 16-bit lookup) goes to the MN-major variant of the same GEMM
+    nchw = act.is_contiguous() and not act.is_contiguous(memory_format=torch.channels_last) and cout <= 256 \
+        and C % 4 == 0 and (H * W) % 4 == 0
+    if not nchw and not act.is_contiguous(memory_format=torch.channels_last):
+        act = act.contiguous(memory_format=torch.channels_last)
     if weight.numel() != cout * C:
         raise RuntimeError(f"weight must hold (out_channels, {C}) values, got {tuple(weight.shape)}")
     weight = weight.reshape(cout, C).contiguous()
@@ -499,9 +502,10 @@ def conv1x1_channels_last(act: torch.Tensor, weight: torch.Tensor, bias: Optiona
         bias = bias.contiguous()
     out = torch.empty((B, cout, H, W), dtype=torch.float32, device=act.device)
     with _on_device(act.device):
-        _capi.check(_capi.lib().raftcorr_conv1x1_nhwc_fwd(
-            act.data_ptr(), weight.data_ptr(), bias.data_ptr() if bias is not None else None, out.data_ptr(), B,
-            H * W, C, cout, 1 if relu else 0, _stream(act)), "raftcorr_conv1x1_nhwc_fwd")
+        fn, name = ((_capi.lib().raftcorr_conv1x1_nchw_fwd, "raftcorr_conv1x1_nchw_fwd") if nchw else
+                    (_capi.lib().raftcorr_conv1x1_nhwc_fwd, "raftcorr_conv1x1_nhwc_fwd"))
+        _capi.check(fn(act.data_ptr(), weight.data_ptr(), bias.data_ptr() if bias is not None else None, out.data_ptr(), B,
+                       H * W, C, cout, 1 if relu else 0, _stream(act)), name)
     return out
 
 

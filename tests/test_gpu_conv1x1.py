@@ -78,3 +78,28 @@ def test_unsupported_shapes_say_so():
         corr.conv1x1_relu(blk(c), torch.randn(8, 324, 1, 1).cuda())
     with pytest.raises(RuntimeError, match="inference"):
         corr.conv1x1_relu(blk(c), torch.randn(8, 324, 1, 1).cuda().requires_grad_(True))
+
+
+@pytest.mark.parametrize("B,H,W,r,cout", [(2, 24, 40, 4, 256), (1, 55, 128, 4, 256), (2, 23, 44, 3, 96)])
+def test_conv1x1_on_the_default_nchw_lookup(B, H, W, r, cout):
+    """The default inference lookup (16-bit pyramid, plain NCHW output) feeds the same GEMM as an MN-major operand
+    (raftcorr_conv1x1_nchw_fwd): identical to the channels-last variant on the same values, and within the TF32 bar
+    of an exact fp32 convolution of that lookup."""
+    import corr
+    gen = torch.Generator().manual_seed(B * 100 + W)
+    D = 64
+    f1 = torch.randn(B, D, H, W, generator=gen).cuda()
+    f2 = torch.randn(B, D, H, W, generator=gen).cuda()
+    c = coords_for("sigma4", B, H, W, gen).cuda()
+    C = 4 * (2 * r + 1) ** 2
+    w = (torch.randn(cout, C, 1, 1, generator=gen) / C ** 0.5).cuda()
+    b = torch.randn(cout, generator=gen).cuda()
+    with torch.no_grad():
+        lk = corr.CorrBlock(f1, f2, radius=r)(c)                      # bf16 blocked pyramid, lookup16
+        assert lk.is_contiguous()
+        got = corr.conv1x1_relu(lk, w, b)
+        same = corr.conv1x1_relu(lk.contiguous(memory_format=torch.channels_last), w, b)
+    assert got.shape == (B, cout, H, W) and got.is_contiguous()
+    assert torch.equal(got, same)
+    ref = _exact_conv(lk, w, b)
+    assert rel_max(got.cpu().numpy(), ref.cpu().numpy()) <= 3e-3
