@@ -22,6 +22,9 @@ Frame pairs shard by batch across GPUs: no collective on the data path ("scaling
   roofline_build   the volume build against both of its roofs (tensor pipe, HBM write)
   dropin_unchanged the UNMODIFIED reference raft.py (baseline/_ref) with this library's corr.py, and
              with the reference's own corr.py, on the same GPU and frames
+  with_tc_convc1 / graph_replay_batch8
+             the headline step with the lookup's consumer on the tensor cores, and
+             replayed as one CUDA graph (raftcorr_b200.graphed); `value` stays the plain eager step
   cpu_baseline / --impl reference
              the reference's own CPU implementation (unmodified core/raft.py + core/corr.py from
              baseline/_ref, kind "reference"; the oracle's torch restatement in the harness model
@@ -698,6 +701,17 @@ def main():
     # the last step's device -> host copy runs on copy_stream: make the timing stream wait for it before t1
     ms_e2e = timed(step_e2e, args.steps, drain=lambda: torch.cuda.current_stream().wait_stream(copy_stream))
 
+    # the same step with the lookup's consumer (convc1 + bias + ReLU) on the tensor cores, reading the NCHW lookup as an
+    # MN-major operand (needs a two-line edit of update.py, hence not the headline)
+    ms_tcconv = None
+    if args.stock_convc1 and not nhwc_lookup:
+        def step_tcconv():
+            with torch.no_grad():
+                return model(dev1, dev2, factory, iters=ITERS, upsampler=upsampler, convc1_fn=raftcorr_dropin.conv1x1_relu)[1]
+        for _ in range(2):
+            step_tcconv()
+        ms_tcconv = timed(step_tcconv, args.steps) / args.steps
+
     # kernel shares: the build (pack + tcgen05 GEMM with the pooled epilogue) once per step, timed on its own with the
     # operands rotated so that no launch finds its inputs or outputs in L2
     fms = [(torch.randn(BATCH_PER_GPU, 256, IMG_H // 8, IMG_W // 8, device=dev),
@@ -793,6 +807,9 @@ def main():
                     "corr_path_share_of_step": (build_ms + ITERS * lookup_avg_ms) / (ms_total / args.steps)},
         "clocks": clocks,
     }
+    if ms_tcconv is not None:
+        line["with_tc_convc1"] = {"ms_per_step": ms_tcconv, "frame_pairs_per_s": BATCH_PER_GPU * n_gpus / (ms_tcconv * 1e-3),
+                                  "convc1": "raftcorr_conv1x1_nchw_fwd on the NCHW lookup (update.py edited as in INTEGRATION.md 2c)"}
     if n_gpus == 1:
         line["other_configs"] = measure_other_configs(dev, peak, model, (dev1, dev2))
         if "latency_batch1" in line["other_configs"]:
