@@ -106,8 +106,9 @@ def ncu_traffic_per_launch(kernel_key: str):
 
 def measure_write_only_gbs(dev, gib: int = 2, reps: int = 6):
     """What this GPU's HBM takes when a kernel only writes (the build's situation: 1.0 GB of pyramid out, 58 MB of
-    operands in): a 2 GiB memset, best of `reps`.  MEASURED_PEAKS.json's hbm_gbs is a copy (half reads)."""
-    buf = torch.empty(gib << 30, dtype=torch.uint8, device=dev)
+    operands in): a 2 GiB fill of 4-byte elements, best of `reps` (torch's 1-byte fill kernel is itself slow, 3.9 TB/s;
+    tools/probe/write_roof_probe.cu: cudaMemsetAsync 7.3 TB/s, plain 16-byte stores 6.9-7.0, TMA bulk stores 6.4)."""
+    buf = torch.empty((gib << 30) // 4, dtype=torch.float32, device=dev)
     buf.zero_()
     best = 1e9
     for _ in range(reps):
@@ -766,8 +767,9 @@ def main():
                    "which": "bf16 dense, cuBLAS 8192^3 (MEASURED_PEAKS.json)" if peaks_all else "fallback"},
         "hbm": {"achieved_gbs": build_gbs, "peak": peak, "frac": build_gbs / peak},
         "hbm_write_only": {"peak": write_only_gbs, "frac": build_gbs / write_only_gbs,
-                           "how": "2 GiB torch memset on this GPU, best of 6: the roof of a kernel that only writes"},
-        "bound": "tensor" if build_tflops / tf_sust >= build_gbs / write_only_gbs else "hbm-write",
+                           "how": "2 GiB fill of 4-byte elements on this GPU, best of 6: what a kernel that only writes can reach"},
+        "bound": "neither roof: epilogue-limited (DESIGN.md 3.1)" if max(build_tflops / tf_sust, build_gbs / write_only_gbs) < 0.7
+                 else ("tensor" if build_tflops / tf_sust >= build_gbs / write_only_gbs else "hbm-write"),
     }
     h2d = 2 * BATCH_PER_GPU * 3 * IMG_H * IMG_W * 4
     d2h = BATCH_PER_GPU * 2 * IMG_H * IMG_W * 4
