@@ -97,7 +97,7 @@ int raftcorr_build_pyramid_noalloc(const float* fmap1, const float* fmap2, int B
                                    void* stream);
 
 /* ---- (1b) the same pyramid in 16-bit storage: core/corr.py:21-27 stores fp32, which makes
- *      the build HBM-write bound (5.3 B written per 512 flop) and the lookup read 4-byte pixels out of 64-byte
+ *      the build write 5.3 B per 512 flop (2 GB at configs[1]) and the lookup read 4-byte pixels out of 64-byte
  *      DRAM granules.  Here every level holds bfloat16 pixels in blocks of 4 rows x 8 columns = 64 bytes (one
  *      DRAM granule; a 10x10 window touches ~7 of them instead of ~13 row pieces):
  *        pixel (y, x) of image n lives at byte  n*image_stride + ((y>>2)*blocks_x + (x>>3))*64 + (y&3)*16 + (x&7)*2
